@@ -1,0 +1,166 @@
+// rt_kernels.cuh — the __global__ entry points (sm_100a). One thread = one pixel (all of its AA
+// samples, summed in the reference's order); a warp covers an 8x4 pixel patch and a 128-thread
+// CTA a 16x8 tile so that the threads of a warp walk the same nodes and hit the same leaves.
+// FP64 CUDA-core arithmetic only (no dense contraction on this path → no tensor cores).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "rt_shade.cuh"
+
+namespace rtk {
+
+struct RenderParams {
+  uint32_t row_begin, row_end;  // frame rows rendered by this call
+  uint32_t tile_rows, rank, nranks;
+  uint32_t owned_rows;          // rows of the launch domain (owned tiles * tile_rows)
+  uint32_t aa, average;
+  int32_t max_depth;
+};
+
+// counters[0..3] rays primary/shadow/reflect/refract, [4] overflow pixels, [5] NaN pixels
+__device__ __forceinline__ void flush_counters(const RayCounters& rc, uint32_t err, unsigned long long* counters) {
+  unsigned a = rc.primary, b = rc.shadow, c = rc.reflect, d = rc.refract;
+  unsigned e = (err & ERR_OVERFLOW) ? 1u : 0u, f = (err & ERR_NAN) ? 1u : 0u;
+  unsigned mask = __activemask();
+  a = __reduce_add_sync(mask, a);
+  b = __reduce_add_sync(mask, b);
+  c = __reduce_add_sync(mask, c);
+  d = __reduce_add_sync(mask, d);
+  e = __reduce_add_sync(mask, e);
+  f = __reduce_add_sync(mask, f);
+  int leader = __ffs(mask) - 1;
+  if ((int)(threadIdx.x & 31) == leader) {
+    if (a) atomicAdd(counters + 0, (unsigned long long)a);
+    if (b) atomicAdd(counters + 1, (unsigned long long)b);
+    if (c) atomicAdd(counters + 2, (unsigned long long)c);
+    if (d) atomicAdd(counters + 3, (unsigned long long)d);
+    if (e) atomicAdd(counters + 4, (unsigned long long)e);
+    if (f) atomicAdd(counters + 5, (unsigned long long)f);
+  }
+}
+
+template <bool HAS_CSG, bool FAITHFUL>
+__global__ void __launch_bounds__(128) render_kernel(SceneView S, CameraD cam, RenderParams P, double* __restrict__ out,
+                                                     unsigned long long* __restrict__ counters) {
+  // 16x8 tile per CTA; warp w → 8x4 patch (w&1, w>>1); lane → (lane&7, lane>>3)
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  const uint32_t px = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
+  const uint32_t oy = blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
+  if (px >= cam.hsize || oy >= P.owned_rows) return;
+  // owned row index → frame row: tile (rank + k*nranks), row within tile
+  const uint32_t k = oy / P.tile_rows, r = oy - k * P.tile_rows;
+  const uint32_t py = (P.rank + k * P.nranks) * P.tile_rows + r;
+  if (py < P.row_begin || py >= P.row_end) return;
+
+  Scratch<HAS_CSG> scratch;
+  RayCounters rc = {0u, 0u, 0u, 0u};
+  uint32_t err = 0;
+  V3 c = render_pixel<HAS_CSG, FAITHFUL>(S, cam, px, py, P.aa, P.average != 0, P.max_depth, scratch, rc, &err);
+  double* o = out + ((size_t)py * cam.hsize + px) * 3;  // Canvas::pixel_idx, canvas.rs:44-48
+  o[0] = c.x;
+  o[1] = c.y;
+  o[2] = c.z;
+  flush_counters(rc, err, counters);
+}
+
+// World::color_at for a batch of rays (debug / known-answer entry)
+template <bool HAS_CSG, bool FAITHFUL>
+__global__ void __launch_bounds__(128) trace_kernel(SceneView S, size_t n, const double* __restrict__ origins,
+                                                    const double* __restrict__ dirs, int remaining,
+                                                    double* __restrict__ rgb, double* __restrict__ t_out,
+                                                    unsigned long long* __restrict__ counters) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  Scratch<HAS_CSG> scratch;
+  RayCounters rc = {0u, 0u, 0u, 0u};
+  uint32_t err = 0;
+  RayD r;
+  r.o = v3(origins[3 * i], origins[3 * i + 1], origins[3 * i + 2]);
+  r.d = v3(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]);
+  double t = -1.0;
+  rc.primary++;
+  V3 c = color_at<HAS_CSG, FAITHFUL>(S, r, remaining, scratch, rc, &err, &t);
+  if (rgb) { rgb[3 * i] = c.x; rgb[3 * i + 1] = c.y; rgb[3 * i + 2] = c.z; }
+  if (t_out) t_out[i] = t;
+  flush_counters(rc, err, counters);
+}
+
+// prepare_computations for one ray (debug / known-answer entry); out[20] as documented in rtc.h
+template <bool HAS_CSG>
+__global__ void probe_kernel(SceneView S, RayD ray, double* __restrict__ out, unsigned long long* __restrict__ counters) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  Scratch<HAS_CSG> scratch;
+  uint32_t err = 0;
+  for (int i = 0; i < 20; i++) out[i] = 0.0;
+  ClosestHit ch;
+  ch.init();
+  walk_scene<HAS_CSG, true>(S, ray, ch, scratch.csg(), &err);
+  if (ch.best_node >= 0) {
+    rtc_node nd = load_node(S.nodes + ch.best_node);
+    Comps c;
+    prepare(S, ray, ch.best_t, ch.best_node, nd, c);
+    NegCollect nc;
+    nc.init(&scratch.neg, &err);
+    walk_scene<HAS_CSG, true>(S, ray, nc, scratch.csg(), &err);
+    containers_n1n2(S, scratch.neg, ch.best_node, c.n1, c.n2, &err);
+    out[0] = 1.0; out[1] = c.t;
+    out[2] = c.point.x; out[3] = c.point.y; out[4] = c.point.z;
+    out[5] = c.normalv.x; out[6] = c.normalv.y; out[7] = c.normalv.z;
+    out[8] = c.over_point.x; out[9] = c.over_point.y; out[10] = c.over_point.z;
+    out[11] = c.under_point.x; out[12] = c.under_point.y; out[13] = c.under_point.z;
+    out[14] = c.reflectv.x; out[15] = c.reflectv.y; out[16] = c.reflectv.z;
+    out[17] = c.n1; out[18] = c.n2; out[19] = c.inside ? 1.0 : 0.0;
+  }
+  RayCounters rc = {0u, 0u, 0u, 0u};
+  flush_counters(rc, err, counters);
+}
+
+template <bool HAS_CSG>
+__global__ void shadow_kernel(SceneView S, V3 point, int light, int* __restrict__ out,
+                              unsigned long long* __restrict__ counters) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  Scratch<HAS_CSG> scratch;
+  uint32_t err = 0;
+  const rtc_light* L = S.lights + light;
+  V3 lp = v3(L->position[0], L->position[1], L->position[2]);
+  out[0] = is_shadowed<HAS_CSG, true>(S, point, lp, scratch.csg(), &err) ? 1 : 0;
+  RayCounters rc = {0u, 0u, 0u, 0u};
+  flush_counters(rc, err, counters);
+}
+
+// image/ppm.rs:73-75: (v * 255.0).round() as u8 — round half away from zero, saturating, NaN → 0
+__global__ void quantize_kernel(const double* __restrict__ rgb, size_t n, uint8_t* __restrict__ out) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    double r = round(rgb[i] * 255.0);
+    uint8_t q;
+    if (r != r) q = 0;
+    else if (r <= 0.0) q = 0;
+    else if (r >= 255.0) q = 255;
+    else q = (uint8_t)r;
+    out[i] = q;
+  }
+}
+
+// FP64 roofline denominators. 8 independent chains per thread.
+template <bool FUSED>
+__global__ void __launch_bounds__(256) fp64_peak_kernel(double* __restrict__ out, int iters, double b, double c) {
+  double a0 = threadIdx.x * 1e-3, a1 = a0 + 1.0, a2 = a0 + 2.0, a3 = a0 + 3.0;
+  double a4 = a0 + 4.0, a5 = a0 + 5.0, a6 = a0 + 6.0, a7 = a0 + 7.0;
+  for (int i = 0; i < iters; i++) {
+    if (FUSED) {
+      a0 = __fma_rn(a0, b, c); a1 = __fma_rn(a1, b, c); a2 = __fma_rn(a2, b, c); a3 = __fma_rn(a3, b, c);
+      a4 = __fma_rn(a4, b, c); a5 = __fma_rn(a5, b, c); a6 = __fma_rn(a6, b, c); a7 = __fma_rn(a7, b, c);
+    } else {
+      a0 = __dadd_rn(__dmul_rn(a0, b), c); a1 = __dadd_rn(__dmul_rn(a1, b), c);
+      a2 = __dadd_rn(__dmul_rn(a2, b), c); a3 = __dadd_rn(__dmul_rn(a3, b), c);
+      a4 = __dadd_rn(__dmul_rn(a4, b), c); a5 = __dadd_rn(__dmul_rn(a5, b), c);
+      a6 = __dadd_rn(__dmul_rn(a6, b), c); a7 = __dadd_rn(__dmul_rn(a7, b), c);
+    }
+  }
+  double s = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+  if (s == 123.456) out[0] = s;  // keep the chains alive
+}
+
+}  // namespace rtk

@@ -1,0 +1,435 @@
+// rt_shade.cuh — hit-point precompute, Phong lighting, shadows and the Whitted recursion rewritten
+// as a bounded iterative loop with an explicit per-thread frame stack that keeps the reference's
+// exact evaluation ORDER and ASSOCIATION:  (surface + reflected·k) + refracted·k'.
+//
+// Reference (relative to raytracer/src): world.rs:40-134 (shade_hit, color_at, is_shadowed,
+// reflected_color, refracted_color), geometry/intersection.rs:53-105,147-162 (prepare_computations,
+// schlick), geometry/mod.rs:51-56 (normal_at), material.rs:38-82 (lighting), pattern/*.rs,
+// camera.rs:57-126 (ray_for_pixel, rays_for_pixel, get_offsets), color.rs:26-33 (average).
+#pragma once
+#include "rt_walk.cuh"
+
+namespace rtk {
+
+constexpr int MAX_FRAMES = 8;  // max_depth + 1 <= MAX_FRAMES
+
+struct RayCounters {
+  uint32_t primary, shadow, reflect, refract;
+};
+
+struct Comps {  // intersection.rs:132-144
+  V3 point, over_point, under_point, eyev, normalv, reflectv;
+  double t, n1, n2;
+  int32_t node;
+  bool inside;
+};
+
+// Per-thread scratch that lives in local memory.
+template <bool HAS_CSG>
+struct Scratch;
+template <>
+struct Scratch<false> {
+  HitList neg;
+  RTC_HD CsgScratch* csg() { return nullptr; }
+};
+template <>
+struct Scratch<true> {
+  HitList neg;
+  CsgScratch cs;
+  RTC_HD CsgScratch* csg() { return &cs; }
+};
+
+// *_local_normal_at for every leaf kind (sphere.rs:64, plane.rs:62, cube.rs:95-105,
+// cylinder.rs:121-130, cone.rs:136-149, triangle.rs:92, smooth_triangle.rs:98-102).
+RTC_HD V3 local_normal(const SceneView& S, const rtc_node& nd, V3 p, int32_t node, const RayD& world_ray) {
+  switch (nd.kind) {
+    case RTC_SPHERE: return v3(p.x - 0.0, p.y - 0.0, p.z - 0.0);
+    case RTC_PLANE: return v3(0.0, 1.0, 0.0);
+    case RTC_CUBE: {
+      double ax = fabs(p.x), ay = fabs(p.y), az = fabs(p.z);
+      double maxc = fmax(fmax(ax, ay), az);
+      if (feq(maxc, ax)) return v3(p.x, 0.0, 0.0);
+      if (feq(maxc, ay)) return v3(0.0, p.y, 0.0);
+      return v3(0.0, 0.0, p.z);
+    }
+    case RTC_CYLINDER: {
+      const double* lim = S.limits + 2 * nd.aux;
+      double dist = p.x * p.x + p.z * p.z;
+      if (dist < 1.0 && p.y >= RTC_LDG(lim + 1) - EPS) return v3(0.0, 1.0, 0.0);
+      if (dist < 1.0 && p.y <= RTC_LDG(lim) + EPS) return v3(0.0, -1.0, 0.0);
+      return v3(p.x, 0.0, p.z);
+    }
+    case RTC_CONE: {
+      const double* lim = S.limits + 2 * nd.aux;
+      double dist = p.x * p.x + p.z * p.z;
+      if (dist < 1.0 && p.y >= RTC_LDG(lim + 1) - EPS) return v3(0.0, 1.0, 0.0);  // dist<1.0: cone.rs:138
+      if (dist < 1.0 && p.y <= RTC_LDG(lim) + EPS) return v3(0.0, -1.0, 0.0);
+      double y = sqrt(p.x * p.x + p.z * p.z);
+      if (p.y > 0.0) y = -y;
+      return v3(p.x, y, p.z);
+    }
+    case RTC_TRIANGLE: {
+      const double* nn = S.tri_normals + 9 * (size_t)nd.aux;
+      return v3(RTC_LDG(nn), RTC_LDG(nn + 1), RTC_LDG(nn + 2));
+    }
+    case RTC_SMOOTH_TRIANGLE: {
+      // u,v of the hit: re-run the (deterministic) triangle test on the same object-space ray
+      RayD lr = leaf_local_ray(S, node, world_ray);
+      double t, u = 0.0, v = 0.0;
+      isect_triangle(lr, S.tri_geom + 9 * (size_t)nd.aux, t, u, v);
+      const double* nn = S.tri_normals + 9 * (size_t)nd.aux;
+      V3 n1 = v3(RTC_LDG(nn), RTC_LDG(nn + 1), RTC_LDG(nn + 2));
+      V3 n2 = v3(RTC_LDG(nn + 3), RTC_LDG(nn + 4), RTC_LDG(nn + 5));
+      V3 n3 = v3(RTC_LDG(nn + 6), RTC_LDG(nn + 7), RTC_LDG(nn + 8));
+      return n2 * u + n3 * v + n1 * (1.0 - u - v);
+    }
+    default: return v3(0.0, 0.0, 0.0);
+  }
+}
+
+// Containers walk for n1/n2 (intersection.rs:61-90). Every list entry before the hit has t < 0;
+// `neg` holds them sorted. Objects toggle by VALUE equality → eq_class.
+RTC_HD void containers_n1n2(const SceneView& S, const HitList& neg, int32_t hit_node, double& n1, double& n2,
+                            uint32_t* err) {
+  int32_t cont[HIT_CAP];
+  int nc = 0;
+  auto toggle = [&](int32_t node) {
+    int32_t cls = RTC_LDG(&S.nodes[node].eq_class);
+    int k = 0;
+    for (; k < nc; k++)
+      if (RTC_LDG(&S.nodes[cont[k]].eq_class) == cls) break;
+    if (k < nc) {
+      for (int m = k; m + 1 < nc; m++) cont[m] = cont[m + 1];
+      nc--;
+    } else if (nc < HIT_CAP) {
+      cont[nc++] = node;
+    } else {
+      *err |= ERR_OVERFLOW;
+    }
+  };
+  auto last_index = [&]() -> double {
+    if (nc == 0) return 1.0;
+    int32_t m = RTC_LDG(&S.nodes[cont[nc - 1]].material);
+    return RTC_LDG(&S.materials[m].refractive_index);
+  };
+  for (int a = 0; a < neg.n; a++) toggle(neg.node[a]);
+  n1 = last_index();
+  toggle(hit_node);
+  n2 = last_index();
+}
+
+// Intersection::prepare_computations (intersection.rs:53-105) without the containers part.
+RTC_HD void prepare(const SceneView& S, const RayD& ray, double t, int32_t node, const rtc_node& nd, Comps& c) {
+  c.t = t;
+  c.node = node;
+  c.point = ray_position(ray, t);
+  c.eyev = -ray.d;
+  const double* inv = S.xforms + 12 * (size_t)nd.xform;
+  V3 local_point = xf_point(inv, c.point);                       // geometry/mod.rs:52
+  V3 ln = local_normal(S, nd, local_point, node, ray);           // :53
+  V3 n = normalize(xf_vector_transposed(inv, ln));               // :54-55
+  c.inside = false;
+  if (dot(n, c.eyev) < 0.0) {
+    c.inside = true;
+    n = -n;
+  }
+  c.normalv = n;
+  c.over_point = c.point + n * EPS;
+  c.under_point = c.point - n * EPS;
+  c.reflectv = reflect(ray.d, n);
+  c.n1 = -1.0;
+  c.n2 = -1.0;
+}
+
+RTC_HD long long as_isize(double v) {  // Rust `as isize`: saturating, NaN → 0
+  if (v != v) return 0;
+  if (v >= 9223372036854775807.0) return 9223372036854775807LL;
+  if (v <= -9223372036854775808.0) return (-9223372036854775807LL - 1LL);
+  return (long long)v;
+}
+
+// Pattern::color_at_shape (pattern/mod.rs:39-49)
+RTC_HD V3 pattern_color(const SceneView& S, int32_t pat, const double* leaf_inv, V3 world_point) {
+  const rtc_pattern* P = S.patterns + pat;
+  V3 op = xf_point(leaf_inv, world_point);
+  V3 p = xf_point(P->inverse, op);
+  V3 a = v3(RTC_LDG(&P->a[0]), RTC_LDG(&P->a[1]), RTC_LDG(&P->a[2]));
+  V3 b = v3(RTC_LDG(&P->b[0]), RTC_LDG(&P->b[1]), RTC_LDG(&P->b[2]));
+  switch (RTC_LDG(&P->kind)) {
+    case RTC_PAT_TEST: return p;                                                  // test_pattern.rs:7-9
+    case RTC_PAT_STRIPE: return fmod(floor(p.x), 2.0) == 0.0 ? a : b;             // stripe.rs:14-20
+    case RTC_PAT_GRADIENT: {                                                      // gradient.rs:14-18
+      V3 distance = b - a;
+      double fraction = p.x - floor(p.x);
+      return a + distance * fraction;
+    }
+    case RTC_PAT_RING: {                                                          // ring.rs:14-21
+      double distance = floor(sqrt(p.x * p.x + p.z * p.z));
+      return fmod(distance, 2.0) == 0.0 ? a : b;
+    }
+    default: {                                                                    // checkers.rs:14-21
+      double distance = floor(p.x) + floor(p.y) + floor(p.z);
+      return as_isize(distance) % 2 == 0 ? a : b;
+    }
+  }
+}
+
+struct MatD {  // material scalars pulled into registers
+  V3 color;
+  double ambient, diffuse, specular, shininess, reflective, transparency;
+  int32_t pattern;
+};
+RTC_HD MatD load_material(const SceneView& S, int32_t m) {
+  const rtc_material* M = S.materials + m;
+  MatD r;
+  r.color = v3(RTC_LDG(&M->color[0]), RTC_LDG(&M->color[1]), RTC_LDG(&M->color[2]));
+  r.ambient = RTC_LDG(&M->ambient);
+  r.diffuse = RTC_LDG(&M->diffuse);
+  r.specular = RTC_LDG(&M->specular);
+  r.shininess = RTC_LDG(&M->shininess);
+  r.reflective = RTC_LDG(&M->reflective);
+  r.transparency = RTC_LDG(&M->transparency);
+  r.pattern = RTC_LDG(&M->pattern);
+  return r;
+}
+
+// Material::lighting (material.rs:38-82); `color` is the pattern/material colour at over_point.
+RTC_HD V3 lighting(const MatD& m, V3 color, V3 light_pos, V3 light_int, V3 point, V3 eyev, V3 normalv, bool in_shadow) {
+  V3 effective = color * light_int;
+  V3 lightv = normalize(light_pos - point);
+  V3 ambient = effective * m.ambient;
+  if (in_shadow) return ambient;
+  double ldn = dot(lightv, normalv);
+  V3 diffuse = v3(0.0, 0.0, 0.0), specular = v3(0.0, 0.0, 0.0);
+  if (!(ldn < 0.0)) {
+    diffuse = effective * m.diffuse * ldn;
+    V3 reflectv = reflect(-lightv, normalv);
+    double rde = dot(reflectv, eyev);
+    if (!(rde <= 0.0)) {
+      double factor = pow(rde, m.shininess);
+      specular = light_int * m.specular * factor;
+    }
+  }
+  return ambient + diffuse + specular;
+}
+
+// Computations::schlick (intersection.rs:147-162)
+RTC_HD double schlick(const Comps& c) {
+  double cs = dot(c.eyev, c.normalv);
+  if (c.n1 > c.n2) {
+    double n = c.n1 / c.n2;
+    double sin2_t = n * n * (1.0 - cs * cs);
+    if (sin2_t > 1.0) return 1.0;
+    cs = sqrt(1.0 - sin2_t);
+  }
+  double q = (c.n1 - c.n2) / (c.n1 + c.n2);
+  double r0 = q * q;
+  double x = 1.0 - cs;
+  double x2 = x * x;
+  double x4 = x2 * x2;
+  return r0 + (1.0 - r0) * (x * x4);
+}
+
+// World::is_shadowed (world.rs:95-105)
+template <bool HAS_CSG, bool FAITHFUL>
+RTC_HD bool is_shadowed(const SceneView& S, V3 point, V3 light_pos, CsgScratch* cs, uint32_t* err) {
+  V3 v = light_pos - point;
+  double distance = magnitude(v);
+  RayD r;
+  r.o = point;
+  r.d = normalize(v);
+  ShadowHit sh;
+  sh.init(distance);
+  walk_scene<HAS_CSG, FAITHFUL>(S, r, sh, cs, err);
+  return sh.found;
+}
+
+struct Frame {
+  V3 surface;      // Σ lights
+  V3 reflected;    // reflected_color result
+  RayD refr_ray;   // pending refraction ray
+  double reflective, transparency, reflectance;
+  uint8_t state;   // 1: waiting for reflection child, 2: waiting for refraction child
+  uint8_t need_refract, use_schlick, _pad;
+};
+
+// World::color_at(ray, remaining = max_depth) (world.rs:70-81), iteratively.
+template <bool HAS_CSG, bool FAITHFUL>
+RTC_HD V3 color_at(const SceneView& S, RayD ray, int max_depth, Scratch<HAS_CSG>& scratch, RayCounters& rc,
+                   uint32_t* err, double* t_out = nullptr) {
+  Frame frames[MAX_FRAMES];
+  int sp = 0;                 // current frame index == depth of the ray being evaluated
+  int remaining = max_depth;
+  V3 result = v3(0.0, 0.0, 0.0);
+  CsgScratch* cs = scratch.csg();
+  for (;;) {
+    // ---- evaluate color_at(ray, remaining) up to the point where it needs a child --------------
+    bool need_child = false;
+    {
+      ClosestHit ch;
+      ch.init();
+      walk_scene<HAS_CSG, FAITHFUL>(S, ray, ch, cs, err);
+      if (t_out && sp == 0) *t_out = ch.best_node >= 0 ? ch.best_t : -1.0;
+      if (ch.best_node < 0) {
+        result = v3(0.0, 0.0, 0.0);  // Color::black()
+      } else {
+        rtc_node nd = load_node(S.nodes + ch.best_node);
+        MatD m = load_material(S, nd.material);
+        Comps c;
+        prepare(S, ray, ch.best_t, ch.best_node, nd, c);
+        Frame& f = frames[sp];
+        // shade_hit: surface = Σ lighting, in light order, from (0,0,0)   (world.rs:41-58)
+        V3 surface = v3(0.0, 0.0, 0.0);
+        const double* leaf_inv = S.xforms + 12 * (size_t)nd.xform;
+        V3 color = m.pattern >= 0 ? pattern_color(S, m.pattern, leaf_inv, c.over_point) : m.color;
+        for (int li = 0; li < S.n_lights; li++) {
+          const rtc_light* L = S.lights + li;
+          V3 lp = v3(RTC_LDG(&L->position[0]), RTC_LDG(&L->position[1]), RTC_LDG(&L->position[2]));
+          V3 lint = v3(RTC_LDG(&L->intensity[0]), RTC_LDG(&L->intensity[1]), RTC_LDG(&L->intensity[2]));
+          rc.shadow++;
+          bool shadowed = is_shadowed<HAS_CSG, FAITHFUL>(S, c.over_point, lp, cs, err);
+          surface = surface + lighting(m, color, lp, lint, c.over_point, c.eyev, c.normalv, shadowed);
+        }
+        f.surface = surface;
+        f.reflective = m.reflective;
+        f.transparency = m.transparency;
+        bool want_reflect = !(feq(m.reflective, 0.0) || remaining == 0);    // world.rs:108
+        bool want_refract = !(feq(m.transparency, 0.0) || remaining == 0);  // world.rs:117
+        f.use_schlick = (m.reflective > 0.0 && m.transparency > 0.0) ? 1 : 0;  // world.rs:62
+        f.need_refract = 0;
+        f.reflectance = 0.0;
+        if (want_refract || f.use_schlick) {
+          // n1/n2 are only ever consumed by refracted_color and schlick
+          NegCollect nc;
+          nc.init(&scratch.neg, err);
+          walk_scene<HAS_CSG, FAITHFUL>(S, ray, nc, cs, err);
+          containers_n1n2(S, scratch.neg, ch.best_node, c.n1, c.n2, err);
+        }
+        if (f.use_schlick) f.reflectance = schlick(c);
+        if (want_refract) {  // world.rs:121-131
+          double n_ratio = c.n1 / c.n2;
+          double cos_i = dot(c.eyev, c.normalv);
+          double sin2_t = n_ratio * n_ratio * (1.0 - cos_i * cos_i);
+          if (!(sin2_t > 1.0)) {
+            double cos_t = sqrt(1.0 - sin2_t);
+            f.refr_ray.o = c.under_point;
+            f.refr_ray.d = c.normalv * (n_ratio * cos_i - cos_t) - c.eyev * n_ratio;  // not normalised
+            f.need_refract = 1;
+          }
+        }
+        if (want_reflect) {
+          rc.reflect++;
+          f.state = 1;
+          ray.o = c.over_point;
+          ray.d = c.reflectv;
+          need_child = true;
+        } else {
+          f.reflected = v3(0.0, 0.0, 0.0);
+          if (f.need_refract) {
+            rc.refract++;
+            f.state = 2;
+            ray = f.refr_ray;
+            need_child = true;
+          } else {
+            V3 refracted = v3(0.0, 0.0, 0.0);
+            result = f.use_schlick ? f.surface + f.reflected * f.reflectance + refracted * (1.0 - f.reflectance)
+                                   : f.surface + f.reflected + refracted;
+          }
+        }
+      }
+    }
+    if (need_child) {
+      sp++;
+      remaining--;
+      continue;
+    }
+    // ---- return `result` to the parents ---------------------------------------------------------
+    for (;;) {
+      if (sp == 0) return result;
+      sp--;
+      remaining++;
+      Frame& f = frames[sp];
+      if (f.state == 1) {
+        f.reflected = result * f.reflective;  // world.rs:113
+        if (f.need_refract) {
+          rc.refract++;
+          f.state = 2;
+          ray = f.refr_ray;
+          need_child = true;
+          break;
+        }
+        V3 refracted = v3(0.0, 0.0, 0.0);
+        result = f.use_schlick ? f.surface + f.reflected * f.reflectance + refracted * (1.0 - f.reflectance)
+                               : f.surface + f.reflected + refracted;
+      } else {
+        V3 refracted = result * f.transparency;  // world.rs:133
+        result = f.use_schlick ? f.surface + f.reflected * f.reflectance + refracted * (1.0 - f.reflectance)
+                               : f.surface + f.reflected + refracted;
+      }
+    }
+    if (need_child) {
+      sp++;
+      remaining--;
+    }
+  }
+}
+
+struct CameraD {
+  double pixel_size, half_width, half_height;
+  double inv[12];
+  V3 origin;  // inverse * Point::origin(), computed once on the host with the same expression
+  uint32_t hsize, vsize;
+};
+
+// camera.rs:57-90
+RTC_HD RayD ray_for_pixel(const CameraD& cam, uint32_t px, uint32_t py, double ox, double oy) {
+  double xoffset = ((double)px + ox) * cam.pixel_size;
+  double yoffset = ((double)py + oy) * cam.pixel_size;
+  double world_x = cam.half_width - xoffset;
+  double world_y = cam.half_height - yoffset;
+  V3 w = v3(world_x, world_y, -1.0);
+  V3 pixel = v3(cam.inv[0] * w.x + cam.inv[1] * w.y + cam.inv[2] * w.z + cam.inv[3],
+                cam.inv[4] * w.x + cam.inv[5] * w.y + cam.inv[6] * w.z + cam.inv[7],
+                cam.inv[8] * w.x + cam.inv[9] * w.y + cam.inv[10] * w.z + cam.inv[11]);
+  RayD r;
+  r.o = cam.origin;
+  r.d = normalize(pixel - cam.origin);
+  return r;
+}
+
+// camera.rs:92-126: sample s of an `aa`-sample pixel
+RTC_HD void aa_offset(uint32_t aa, uint32_t s, double& ox, double& oy) {
+  switch (aa) {
+    case 2: ox = s == 0 ? 0.25 : 0.75; oy = 0.5; break;
+    case 4: ox = (s & 1) ? 0.75 : 0.25; oy = (s & 2) ? 0.75 : 0.25; break;
+    case 8: {
+      const double xs[8] = {0.25, 0.5, 0.75, 0.25, 0.75, 0.25, 0.5, 0.75};
+      const double ys[8] = {0.25, 0.25, 0.25, 0.5, 0.5, 0.75, 0.75, 0.75};
+      ox = xs[s & 7]; oy = ys[s & 7];
+      break;
+    }
+    case 16: ox = 0.125 + 0.25 * (double)(s & 3); oy = 0.125 + 0.25 * (double)((s >> 2) & 3); break;
+    default: ox = 0.5; oy = 0.5; break;
+  }
+}
+
+// One pixel of Camera::render (aa==1, camera.rs:133-148: colour stored as is) or of
+// render_multithreaded (camera.rs:178-187: Color::average = sequential sum * (1.0/n)).
+template <bool HAS_CSG, bool FAITHFUL>
+RTC_HD V3 render_pixel(const SceneView& S, const CameraD& cam, uint32_t px, uint32_t py, uint32_t aa, bool average,
+                       int max_depth, Scratch<HAS_CSG>& scratch, RayCounters& rc, uint32_t* err) {
+  if (!average) {
+    rc.primary++;
+    return color_at<HAS_CSG, FAITHFUL>(S, ray_for_pixel(cam, px, py, 0.5, 0.5), max_depth, scratch, rc, err);
+  }
+  V3 avg = v3(0.0, 0.0, 0.0);
+  for (uint32_t s = 0; s < aa; s++) {
+    double ox, oy;
+    aa_offset(aa, s, ox, oy);
+    rc.primary++;
+    avg = avg + color_at<HAS_CSG, FAITHFUL>(S, ray_for_pixel(cam, px, py, ox, oy), max_depth, scratch, rc, err);
+  }
+  return avg * (1.0 / (double)aa);
+}
+
+}  // namespace rtk

@@ -1,0 +1,514 @@
+// rtc_api.cu — the C-ABI of include/rtc.h over the sm_100a kernels. Build:
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo --fmad=false -Xcompiler -fPIC,-ffp-contract=off
+//        -shared -o librtc_cuda.so rtc_api.cu
+// No CPU fallback: every compute entry point needs a CUDA device.
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "rt_kernels.cuh"
+
+using namespace rtk;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+#define CUDA_TRY(expr)                                                                          \
+  do {                                                                                          \
+    cudaError_t e_ = (expr);                                                                    \
+    if (e_ != cudaSuccess) {                                                                    \
+      return fail(RTC_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_));            \
+    }                                                                                           \
+  } while (0)
+
+constexpr int N_COUNTERS = 8;
+
+}  // namespace
+
+struct rtc_scene {
+  int device = 0;
+  char* slab = nullptr;  // one device allocation holding every table
+  size_t slab_bytes = 0;
+  SceneView view{};
+  bool has_csg = false;
+  unsigned long long* d_counters = nullptr;
+  double* d_canvas = nullptr;  // cached device canvas for rtc_render
+  size_t canvas_doubles = 0;
+  double* d_probe = nullptr;   // 32 doubles scratch for the debug entries
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  uint32_t launches = 0;
+};
+
+struct rtc_canvas {
+  int device = 0;
+  double* ptr = nullptr;
+  size_t n = 0;
+  bool opened = false;  // came from an IPC handle
+};
+
+namespace {
+
+// Structural validation of a flattened world; also derives csg_parent[] and the CSG nesting depth.
+int validate(const rtc_scene_desc* d, std::vector<int32_t>& csg_parent, bool& has_csg) {
+  if (!d) return fail(RTC_ERR_INVALID, "desc is NULL");
+  if (d->abi_version != RTC_ABI_VERSION) return fail(RTC_ERR_INVALID, "abi_version mismatch");
+  if (d->n_nodes > 0 && !d->nodes) return fail(RTC_ERR_INVALID, "nodes is NULL");
+  if (d->n_nodes > 0x7fffff00u) return fail(RTC_ERR_INVALID, "too many nodes");
+  const int32_t n = (int32_t)d->n_nodes;
+  csg_parent.assign((size_t)n, -1);
+  has_csg = false;
+  // stack of enclosing aggregates: (end index, is_csg, node index)
+  struct Open { int32_t end; bool csg; int32_t node; };
+  std::vector<Open> open;
+  for (int32_t i = 0; i < n; i++) {
+    while (!open.empty() && open.back().end == i) open.pop_back();
+    const rtc_node& nd = d->nodes[i];
+    char where[64];
+    std::snprintf(where, sizeof where, "node %d: ", i);
+    int32_t limit = open.empty() ? n : open.back().end;
+    for (auto it = open.rbegin(); it != open.rend(); ++it)
+      if (it->csg) { csg_parent[(size_t)i] = it->node; break; }
+    if (nd.kind < RTC_SPHERE || nd.kind > RTC_CSG) return fail(RTC_ERR_INVALID, std::string(where) + "bad kind");
+    bool aggregate = nd.kind == RTC_GROUP || nd.kind == RTC_CSG;
+    if (!aggregate) {
+      if (nd.skip != i + 1) return fail(RTC_ERR_INVALID, std::string(where) + "leaf skip must be index+1");
+      if (nd.xform < 0 || (uint32_t)nd.xform >= d->n_xforms) return fail(RTC_ERR_INVALID, std::string(where) + "xform out of range");
+      if (nd.material < 0 || (uint32_t)nd.material >= d->n_materials) return fail(RTC_ERR_INVALID, std::string(where) + "material out of range");
+      if ((nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE) && (nd.aux < 0 || (uint32_t)nd.aux >= d->n_triangles))
+        return fail(RTC_ERR_INVALID, std::string(where) + "triangle index out of range");
+      if ((nd.kind == RTC_CYLINDER || nd.kind == RTC_CONE) && (nd.aux < 0 || (uint32_t)nd.aux >= d->n_limits))
+        return fail(RTC_ERR_INVALID, std::string(where) + "limits index out of range");
+    } else {
+      if (nd.skip <= i || nd.skip > limit) return fail(RTC_ERR_INVALID, std::string(where) + "skip out of range");
+      if (nd.aux < 0 || (uint32_t)nd.aux >= d->n_boxes) return fail(RTC_ERR_INVALID, std::string(where) + "box index out of range");
+      if (nd.kind == RTC_CSG) {
+        has_csg = true;
+        if (nd.xform < 0 || (uint32_t)nd.xform >= d->n_xforms) return fail(RTC_ERR_INVALID, std::string(where) + "xform out of range");
+        if (nd.right <= i + 1 || nd.right >= nd.skip) return fail(RTC_ERR_INVALID, std::string(where) + "CSG right index out of range");
+        if (d->nodes[i + 1].skip != nd.right) return fail(RTC_ERR_INVALID, std::string(where) + "CSG left subtree must end at right");
+        if (d->nodes[nd.right].skip != nd.skip) return fail(RTC_ERR_INVALID, std::string(where) + "CSG right subtree must end at skip");
+        if (((nd.flags >> 8) & 3u) > 2u) return fail(RTC_ERR_INVALID, std::string(where) + "bad CSG op");
+        int depth = 1;
+        for (auto& o : open) depth += o.csg ? 1 : 0;
+        if (depth > CSG_MAX_DEPTH) return fail(RTC_ERR_UNSUPPORTED, std::string(where) + "CSG nesting deeper than 4");
+      }
+      if (nd.skip > i + 1) open.push_back({nd.skip, nd.kind == RTC_CSG, i});
+    }
+    if (nd.skip > limit) return fail(RTC_ERR_INVALID, std::string(where) + "subtree crosses its parent");
+  }
+  for (uint32_t m = 0; m < d->n_materials; m++) {
+    int32_t p = d->materials[m].pattern;
+    if (p >= 0 && (uint32_t)p >= d->n_patterns) return fail(RTC_ERR_INVALID, "material pattern out of range");
+  }
+  return RTC_OK;
+}
+
+size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
+
+template <class K>
+void launch_render(bool has_csg, bool faithful, K&& go) {
+  if (has_csg) { if (faithful) go(std::true_type{}, std::true_type{}); else go(std::true_type{}, std::false_type{}); }
+  else { if (faithful) go(std::false_type{}, std::true_type{}); else go(std::false_type{}, std::false_type{}); }
+}
+
+int read_counters(rtc_scene* s, cudaStream_t stream, rtc_stats* stats) {
+  unsigned long long h[N_COUNTERS];
+  CUDA_TRY(cudaMemcpyAsync(h, s->d_counters, sizeof h, cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(cudaStreamSynchronize(stream));
+  if (stats) {
+    stats->rays_primary = h[0]; stats->rays_shadow = h[1]; stats->rays_reflect = h[2]; stats->rays_refract = h[3];
+    stats->overflow_count = h[4]; stats->nan_count = h[5];
+  }
+  if (h[4]) return fail(RTC_ERR_OVERFLOW, "a bounded intersection list overflowed on the device (CSG/containers, cap 64)");
+  if (h[5]) return fail(RTC_ERR_NAN, "NaN t reached the intersection sort (the reference panics: intersection.rs:113)");
+  return RTC_OK;
+}
+
+int make_camera(const rtc_camera* c, CameraD& cam) {
+  if (!c || c->hsize == 0 || c->vsize == 0) return fail(RTC_ERR_INVALID, "bad camera");
+  cam.pixel_size = c->pixel_size; cam.half_width = c->half_width; cam.half_height = c->half_height;
+  for (int i = 0; i < 12; i++) cam.inv[i] = c->inverse[i];
+  // &self.transform_inverse * Point::origin()  (camera.rs:65; matrix.rs:232-245), same expression
+  const double z = 0.0;
+  volatile double ox = c->inverse[0] * z + c->inverse[1] * z + c->inverse[2] * z + c->inverse[3];
+  volatile double oy = c->inverse[4] * z + c->inverse[5] * z + c->inverse[6] * z + c->inverse[7];
+  volatile double oz = c->inverse[8] * z + c->inverse[9] * z + c->inverse[10] * z + c->inverse[11];
+  cam.origin = v3(ox, oy, oz);
+  cam.hsize = c->hsize; cam.vsize = c->vsize;
+  return RTC_OK;
+}
+
+int make_params(const rtc_camera* c, const rtc_opts* o, RenderParams& P, bool& faithful) {
+  rtc_opts d{};
+  d.aa_samples = 1; d.max_depth = 5;
+  if (o) d = *o;
+  if (!(d.aa_samples == 1 || d.aa_samples == 2 || d.aa_samples == 4 || d.aa_samples == 8 || d.aa_samples == 16))
+    return fail(RTC_ERR_INVALID, "aa_samples must be 1, 2, 4, 8 or 16 (camera.rs:227-233)");
+  if ((int)d.max_depth + 1 > MAX_FRAMES) return fail(RTC_ERR_UNSUPPORTED, "max_depth > 7");
+  P.row_begin = d.row_begin; P.row_end = d.row_end;
+  if (P.row_begin == 0 && P.row_end == 0) P.row_end = c->vsize;
+  if (P.row_end > c->vsize) P.row_end = c->vsize;
+  if (P.row_begin > P.row_end) return fail(RTC_ERR_INVALID, "row_begin > row_end");
+  P.nranks = d.nranks ? d.nranks : 1;
+  P.rank = d.rank;
+  if (P.rank >= P.nranks) return fail(RTC_ERR_INVALID, "rank >= nranks");
+  P.tile_rows = d.tile_rows ? d.tile_rows : 8;
+  uint32_t n_tiles = (c->vsize + P.tile_rows - 1) / P.tile_rows;
+  uint32_t owned_tiles = n_tiles > P.rank ? (n_tiles - P.rank + P.nranks - 1) / P.nranks : 0;
+  P.owned_rows = owned_tiles * P.tile_rows;
+  P.aa = d.aa_samples;
+  P.average = (d.aa_samples > 1 || (d.flags & RTC_OPT_AVERAGE)) ? 1u : 0u;
+  P.max_depth = (int32_t)d.max_depth;
+  faithful = (d.flags & RTC_OPT_FAITHFUL_TRAVERSAL) != 0;
+  return RTC_OK;
+}
+
+int launch_frame(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool faithful, double* out, cudaStream_t stream) {
+  CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, N_COUNTERS * sizeof(unsigned long long), stream));
+  dim3 block(128), grid((cam.hsize + 15) / 16, (P.owned_rows + 7) / 8);
+  CUDA_TRY(cudaEventRecord(s->ev0, stream));
+  if (grid.x > 0 && grid.y > 0) {
+    launch_render(s->has_csg, faithful, [&](auto csg, auto fa) {
+      render_kernel<decltype(csg)::value, decltype(fa)::value><<<grid, block, 0, stream>>>(s->view, cam, P, out, s->d_counters);
+    });
+    s->launches++;
+  }
+  CUDA_TRY(cudaEventRecord(s->ev1, stream));
+  CUDA_TRY(cudaGetLastError());
+  return RTC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* rtc_last_error(void) { return g_err.c_str(); }
+int rtc_abi_version(void) { return RTC_ABI_VERSION; }
+int rtc_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
+  if (!out) return fail(RTC_ERR_INVALID, "out is NULL");
+  *out = nullptr;
+  std::vector<int32_t> csg_parent;
+  bool has_csg = false;
+  int rc = validate(d, csg_parent, has_csg);
+  if (rc) return rc;
+  if (rtc_device_count() <= device || device < 0) return fail(RTC_ERR_CUDA, "no such CUDA device (this library has no CPU fallback)");
+  CUDA_TRY(cudaSetDevice(device));
+
+  // one slab: [nodes | xforms | boxes | limits | tri_geom | tri_normals | materials | patterns | lights | csg_parent]
+  struct Part { const void* src; size_t bytes; size_t off; };
+  Part parts[10] = {
+      {d->nodes, sizeof(rtc_node) * d->n_nodes, 0},
+      {d->xforms, sizeof(double) * 12 * d->n_xforms, 0},
+      {d->boxes, sizeof(double) * 6 * d->n_boxes, 0},
+      {d->limits, sizeof(double) * 2 * d->n_limits, 0},
+      {d->tri_p1e1e2, sizeof(double) * 9 * d->n_triangles, 0},
+      {d->tri_normals, sizeof(double) * 9 * d->n_triangles, 0},
+      {d->materials, sizeof(rtc_material) * d->n_materials, 0},
+      {d->patterns, sizeof(rtc_pattern) * d->n_patterns, 0},
+      {d->lights, sizeof(rtc_light) * d->n_lights, 0},
+      {csg_parent.data(), sizeof(int32_t) * csg_parent.size(), 0}};
+  size_t total = 0;
+  for (auto& p : parts) {
+    if (p.bytes && !p.src) return fail(RTC_ERR_INVALID, "a non-empty table has a NULL pointer");
+    p.off = total;
+    total += align_up(p.bytes);
+  }
+  if (total == 0) total = 256;
+  rtc_scene* s = new rtc_scene();
+  s->device = device;
+  s->has_csg = has_csg;
+  s->slab_bytes = total;
+  auto bail = [&](cudaError_t e, const char* what) {
+    std::string m = std::string(what) + ": " + cudaGetErrorString(e);
+    rtc_scene_destroy(s);
+    return fail(RTC_ERR_CUDA, m);
+  };
+  cudaError_t e;
+  if ((e = cudaMalloc((void**)&s->slab, total)) != cudaSuccess) return bail(e, "cudaMalloc(scene)");
+  if ((e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+  if ((e = cudaEventCreate(&s->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
+  if ((e = cudaEventCreate(&s->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
+  if ((e = cudaMalloc((void**)&s->d_counters, N_COUNTERS * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "cudaMalloc(counters)");
+  if ((e = cudaMalloc((void**)&s->d_probe, 32 * sizeof(double))) != cudaSuccess) return bail(e, "cudaMalloc(probe)");
+  // stage on the host, one H2D copy
+  std::vector<char> stage(total, 0);
+  for (auto& p : parts)
+    if (p.bytes) std::memcpy(stage.data() + p.off, p.src, p.bytes);
+  if ((e = cudaMemcpyAsync(s->slab, stage.data(), total, cudaMemcpyHostToDevice, s->stream)) != cudaSuccess) return bail(e, "cudaMemcpy(scene)");
+  if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return bail(e, "cudaStreamSynchronize");
+  SceneView& v = s->view;
+  v.nodes = (const rtc_node*)(s->slab + parts[0].off);
+  v.xforms = (const double*)(s->slab + parts[1].off);
+  v.boxes = (const double*)(s->slab + parts[2].off);
+  v.limits = (const double*)(s->slab + parts[3].off);
+  v.tri_geom = (const double*)(s->slab + parts[4].off);
+  v.tri_normals = (const double*)(s->slab + parts[5].off);
+  v.materials = (const rtc_material*)(s->slab + parts[6].off);
+  v.patterns = (const rtc_pattern*)(s->slab + parts[7].off);
+  v.lights = (const rtc_light*)(s->slab + parts[8].off);
+  v.csg_parent = (const int32_t*)(s->slab + parts[9].off);
+  v.n_nodes = (int32_t)d->n_nodes;
+  v.n_lights = (int32_t)d->n_lights;
+  v.has_csg = has_csg ? 1 : 0;
+  *out = s;
+  return RTC_OK;
+}
+
+void rtc_scene_destroy(rtc_scene* s) {
+  if (!s) return;
+  cudaSetDevice(s->device);
+  if (s->slab) cudaFree(s->slab);
+  if (s->d_counters) cudaFree(s->d_counters);
+  if (s->d_canvas) cudaFree(s->d_canvas);
+  if (s->d_probe) cudaFree(s->d_probe);
+  if (s->ev0) cudaEventDestroy(s->ev0);
+  if (s->ev1) cudaEventDestroy(s->ev1);
+  if (s->stream) cudaStreamDestroy(s->stream);
+  delete s;
+}
+
+int rtc_render_device(rtc_scene* s, const rtc_camera* camera, const rtc_opts* opts, double* rgb_dev, void* stream_, rtc_stats* stats) {
+  if (!s || !rgb_dev) return fail(RTC_ERR_INVALID, "NULL scene or canvas");
+  auto t0 = std::chrono::steady_clock::now();
+  CameraD cam;
+  RenderParams P;
+  bool faithful = false;
+  int rc = make_camera(camera, cam);
+  if (rc) return rc;
+  rc = make_params(camera, opts, P, faithful);
+  if (rc) return rc;
+  CUDA_TRY(cudaSetDevice(s->device));
+  cudaStream_t stream = (cudaStream_t)stream_;
+  s->launches = 0;
+  rc = launch_frame(s, cam, P, faithful, rgb_dev, stream);
+  if (rc) return rc;
+  if (stats) {
+    rc = rtc_scene_finish(s, stream_, stats);
+    stats->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  }
+  return rc;
+}
+
+int rtc_scene_finish(rtc_scene* s, void* stream_, rtc_stats* stats) {
+  if (!s) return fail(RTC_ERR_INVALID, "NULL scene");
+  CUDA_TRY(cudaSetDevice(s->device));
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (stats) std::memset(stats, 0, sizeof *stats);
+  int rc = read_counters(s, stream, stats);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(RTC_ERR_CUDA, std::string("kernel: ") + cudaGetErrorString(e));
+  if (stats) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, s->ev0, s->ev1) == cudaSuccess) stats->kernel_ms = ms; else cudaGetLastError();
+    stats->launches = s->launches;
+  }
+  return rc;
+}
+
+int rtc_render(rtc_scene* s, const rtc_camera* camera, const rtc_opts* opts, double* rgb_host, rtc_stats* stats) {
+  if (!s || !rgb_host) return fail(RTC_ERR_INVALID, "NULL scene or canvas");
+  auto t0 = std::chrono::steady_clock::now();
+  CameraD cam;
+  RenderParams P;
+  bool faithful = false;
+  int rc = make_camera(camera, cam);
+  if (rc) return rc;
+  rc = make_params(camera, opts, P, faithful);
+  if (rc) return rc;
+  CUDA_TRY(cudaSetDevice(s->device));
+  size_t need = (size_t)cam.hsize * cam.vsize * 3;
+  if (s->canvas_doubles < need) {
+    if (s->d_canvas) cudaFree(s->d_canvas);
+    s->d_canvas = nullptr;
+    s->canvas_doubles = 0;
+    CUDA_TRY(cudaMalloc((void**)&s->d_canvas, need * sizeof(double)));
+    s->canvas_doubles = need;
+  }
+  s->launches = 0;
+  rc = launch_frame(s, cam, P, faithful, s->d_canvas, s->stream);
+  if (rc) return rc;
+  // device → host: only the rows this call rendered (owned tiles clipped to the row range)
+  const size_t row_doubles = (size_t)cam.hsize * 3;
+  if (P.nranks <= 1) {
+    size_t off = (size_t)P.row_begin * row_doubles, cnt = (size_t)(P.row_end - P.row_begin) * row_doubles;
+    if (cnt) CUDA_TRY(cudaMemcpyAsync(rgb_host + off, s->d_canvas + off, cnt * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  } else {
+    for (uint32_t t = P.rank; (size_t)t * P.tile_rows < cam.vsize; t += P.nranks) {
+      uint32_t y0 = t * P.tile_rows, y1 = y0 + P.tile_rows;
+      if (y0 < P.row_begin) y0 = P.row_begin;
+      if (y1 > P.row_end) y1 = P.row_end;
+      if (y0 >= y1) continue;
+      size_t off = (size_t)y0 * row_doubles, cnt = (size_t)(y1 - y0) * row_doubles;
+      CUDA_TRY(cudaMemcpyAsync(rgb_host + off, s->d_canvas + off, cnt * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+    }
+  }
+  rtc_stats local;
+  rc = rtc_scene_finish(s, s->stream, &local);
+  local.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  if (stats) *stats = local;
+  return rc;
+}
+
+int rtc_quantize_device(int device, const double* rgb_dev, size_t n, uint8_t* rgb8_dev, void* stream) {
+  if (!rgb_dev || !rgb8_dev) return fail(RTC_ERR_INVALID, "NULL buffer");
+  CUDA_TRY(cudaSetDevice(device));
+  if (n == 0) return RTC_OK;
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  quantize_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(rgb_dev, n, rgb8_dev);
+  CUDA_TRY(cudaGetLastError());
+  return RTC_OK;
+}
+
+int rtc_trace_rays(rtc_scene* s, size_t n, const double* origins, const double* directions, uint32_t remaining,
+                   double* rgb_out, double* t_out) {
+  if (!s || !origins || !directions) return fail(RTC_ERR_INVALID, "NULL argument");
+  if ((int)remaining + 1 > MAX_FRAMES) return fail(RTC_ERR_UNSUPPORTED, "remaining > 7");
+  if (n == 0) return RTC_OK;
+  CUDA_TRY(cudaSetDevice(s->device));
+  double *d_o = nullptr, *d_d = nullptr, *d_rgb = nullptr, *d_t = nullptr;
+  auto cleanup = [&]() { cudaFree(d_o); cudaFree(d_d); cudaFree(d_rgb); cudaFree(d_t); };
+  cudaError_t e;
+#define TRY_OR_CLEAN(expr) if ((e = (expr)) != cudaSuccess) { cleanup(); return fail(RTC_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e)); }
+  TRY_OR_CLEAN(cudaMalloc((void**)&d_o, 3 * n * sizeof(double)));
+  TRY_OR_CLEAN(cudaMalloc((void**)&d_d, 3 * n * sizeof(double)));
+  TRY_OR_CLEAN(cudaMalloc((void**)&d_rgb, 3 * n * sizeof(double)));
+  TRY_OR_CLEAN(cudaMalloc((void**)&d_t, n * sizeof(double)));
+  TRY_OR_CLEAN(cudaMemcpyAsync(d_o, origins, 3 * n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  TRY_OR_CLEAN(cudaMemcpyAsync(d_d, directions, 3 * n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  TRY_OR_CLEAN(cudaMemsetAsync(s->d_counters, 0, N_COUNTERS * sizeof(unsigned long long), s->stream));
+  unsigned blocks = (unsigned)((n + 127) / 128);
+  if (s->has_csg) trace_kernel<true, true><<<blocks, 128, 0, s->stream>>>(s->view, n, d_o, d_d, (int)remaining, d_rgb, d_t, s->d_counters);
+  else trace_kernel<false, true><<<blocks, 128, 0, s->stream>>>(s->view, n, d_o, d_d, (int)remaining, d_rgb, d_t, s->d_counters);
+  TRY_OR_CLEAN(cudaGetLastError());
+  if (rgb_out) TRY_OR_CLEAN(cudaMemcpyAsync(rgb_out, d_rgb, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  if (t_out) TRY_OR_CLEAN(cudaMemcpyAsync(t_out, d_t, n * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  int rc = read_counters(s, s->stream, nullptr);
+  cleanup();
+#undef TRY_OR_CLEAN
+  return rc;
+}
+
+int rtc_probe_hit(rtc_scene* s, const double* o, const double* dir, double* out20) {
+  if (!s || !o || !dir || !out20) return fail(RTC_ERR_INVALID, "NULL argument");
+  CUDA_TRY(cudaSetDevice(s->device));
+  RayD r;
+  r.o = v3(o[0], o[1], o[2]);
+  r.d = v3(dir[0], dir[1], dir[2]);
+  CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, N_COUNTERS * sizeof(unsigned long long), s->stream));
+  if (s->has_csg) probe_kernel<true><<<1, 32, 0, s->stream>>>(s->view, r, s->d_probe, s->d_counters);
+  else probe_kernel<false><<<1, 32, 0, s->stream>>>(s->view, r, s->d_probe, s->d_counters);
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaMemcpyAsync(out20, s->d_probe, 20 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  return read_counters(s, s->stream, nullptr);
+}
+
+int rtc_is_shadowed(rtc_scene* s, const double* p, uint32_t light_index) {
+  if (!s || !p) return fail(RTC_ERR_INVALID, "NULL argument");
+  if ((int32_t)light_index >= s->view.n_lights) return fail(RTC_ERR_INVALID, "light index out of range");
+  CUDA_TRY(cudaSetDevice(s->device));
+  CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, N_COUNTERS * sizeof(unsigned long long), s->stream));
+  int* d_out = reinterpret_cast<int*>(s->d_probe);
+  if (s->has_csg) shadow_kernel<true><<<1, 32, 0, s->stream>>>(s->view, v3(p[0], p[1], p[2]), (int)light_index, d_out, s->d_counters);
+  else shadow_kernel<false><<<1, 32, 0, s->stream>>>(s->view, v3(p[0], p[1], p[2]), (int)light_index, d_out, s->d_counters);
+  CUDA_TRY(cudaGetLastError());
+  int h = 0;
+  CUDA_TRY(cudaMemcpyAsync(&h, d_out, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+  int rc = read_counters(s, s->stream, nullptr);
+  return rc ? rc : h;
+}
+
+int rtc_canvas_create(int device, size_t n_doubles, rtc_canvas** out) {
+  if (!out || n_doubles == 0) return fail(RTC_ERR_INVALID, "bad canvas size");
+  CUDA_TRY(cudaSetDevice(device));
+  rtc_canvas* c = new rtc_canvas();
+  c->device = device;
+  c->n = n_doubles;
+  cudaError_t e = cudaMalloc((void**)&c->ptr, n_doubles * sizeof(double));
+  if (e != cudaSuccess) { delete c; return fail(RTC_ERR_CUDA, std::string("cudaMalloc(canvas): ") + cudaGetErrorString(e)); }
+  cudaMemset(c->ptr, 0, n_doubles * sizeof(double));
+  *out = c;
+  return RTC_OK;
+}
+int rtc_canvas_export(rtc_canvas* c, unsigned char handle[64]) {
+  if (!c || c->opened) return fail(RTC_ERR_INVALID, "cannot export this canvas");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  cudaIpcMemHandle_t h;
+  CUDA_TRY(cudaSetDevice(c->device));
+  CUDA_TRY(cudaIpcGetMemHandle(&h, c->ptr));
+  std::memcpy(handle, &h, 64);
+  return RTC_OK;
+}
+int rtc_canvas_open(int device, const unsigned char handle[64], size_t n_doubles, rtc_canvas** out) {
+  if (!out) return fail(RTC_ERR_INVALID, "out is NULL");
+  CUDA_TRY(cudaSetDevice(device));
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle, 64);
+  void* p = nullptr;
+  CUDA_TRY(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  rtc_canvas* c = new rtc_canvas();
+  c->device = device; c->ptr = (double*)p; c->n = n_doubles; c->opened = true;
+  *out = c;
+  return RTC_OK;
+}
+double* rtc_canvas_ptr(rtc_canvas* c) { return c ? c->ptr : nullptr; }
+int rtc_canvas_download(rtc_canvas* c, double* host, size_t off, size_t n) {
+  if (!c || !host || off + n > c->n) return fail(RTC_ERR_INVALID, "bad canvas range");
+  CUDA_TRY(cudaSetDevice(c->device));
+  CUDA_TRY(cudaMemcpy(host, c->ptr + off, n * sizeof(double), cudaMemcpyDeviceToHost));
+  return RTC_OK;
+}
+void rtc_canvas_destroy(rtc_canvas* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->opened) cudaIpcCloseMemHandle(c->ptr); else cudaFree(c->ptr);
+  delete c;
+}
+
+int rtc_measure_fp64(int device, int fused, double* gflops_out) {
+  if (!gflops_out) return fail(RTC_ERR_INVALID, "NULL out");
+  CUDA_TRY(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  double* d = nullptr;
+  CUDA_TRY(cudaMalloc((void**)&d, 64));
+  cudaEvent_t a, b;
+  CUDA_TRY(cudaEventCreate(&a));
+  CUDA_TRY(cudaEventCreate(&b));
+  const int iters = 8192, threads = 256, blocks = prop.multiProcessorCount * 8;
+  double best = 0.0;
+  for (int rep = 0; rep < 5; rep++) {
+    cudaEventRecord(a);
+    if (fused) fp64_peak_kernel<true><<<blocks, threads>>>(d, iters, 1.0000001, 1e-9);
+    else fp64_peak_kernel<false><<<blocks, threads>>>(d, iters, 1.0000001, 1e-9);
+    cudaEventRecord(b);
+    cudaError_t e = cudaEventSynchronize(b);
+    if (e != cudaSuccess) { cudaFree(d); return fail(RTC_ERR_CUDA, cudaGetErrorString(e)); }
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, a, b);
+    double flops = (double)blocks * threads * (double)iters * 8.0 * 2.0;
+    double g = flops / (ms * 1e-3) / 1e9;
+    if (rep > 0 && g > best) best = g;
+  }
+  cudaEventDestroy(a);
+  cudaEventDestroy(b);
+  cudaFree(d);
+  *gflops_out = best;
+  return RTC_OK;
+}
+
+}  // extern "C"
