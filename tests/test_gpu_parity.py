@@ -1,0 +1,149 @@
+"""GPU tier (B200): the CUDA path through the C-ABI (librtc_cuda.so) vs the oracle on the same seeded
+scenes. Bar (north_star): >= 99.9 % identical 8-bit pixels, no channel off by more than 1, linear
+colour within 1e-6 — and identical per-kind ray counts, which catches control-flow divergence that a
+colour tolerance could hide. Everything except libm-vs-CUDA pow() (specular term, <= 2 ulp) is
+expected to be bit-exact."""
+import ctypes as C
+import importlib
+
+import numpy as np
+import pytest
+
+from conftest import compare_images
+from scene_cases import MESH_CASES, SMALL_CASES, case_id
+
+scenes = importlib.import_module("raytracer-challenge-rs_b200.scenes")
+pytestmark = pytest.mark.gpu
+
+LIN_TOL = 1e-6      # north_star: linear colour within 1e-6
+EXPECT_LIN = 1e-12  # what the design actually delivers (pow ulps only)
+
+
+@pytest.mark.parametrize("case", SMALL_CASES + MESH_CASES, ids=case_id)
+def test_render_matches_oracle(case, pkg, prod, orc):
+    name, kw, aa = case
+    wo, co = scenes.CONFIGS[name](orc.api, **kw)
+    wp, cp = scenes.CONFIGS[name](prod, **kw)
+    want, iw = orc.render(co, wo, aa=aa, threads=0 if aa == 1 else 8)
+    got, st, _ = pkg.render(cp, wp, device=0, aa=aa)
+    assert st.overflow_count == 0 and st.nan_count == 0
+    assert (st.rays_primary, st.rays_shadow, st.rays_reflect, st.rays_refract) == \
+        (iw["rays_primary"], iw["rays_shadow"], iw["rays_reflect"], iw["rays_refract"])
+    frac, max8, lin = compare_images(got, want, orc.quantize)
+    assert frac >= 0.999 and max8 <= 1 and lin <= LIN_TOL, (frac, max8, lin)
+    assert lin <= EXPECT_LIN, lin
+    # device quantiser == reference quantiser on this frame
+    assert np.array_equal(pkg.quantize(got), orc.quantize(got))
+    # PPM text identical to the oracle's canvas_to_ppm of its own frame when the 8-bit images agree
+    if frac == 1.0:
+        assert pkg.canvas_to_ppm(got) == orc.canvas_to_ppm(want)
+
+
+@pytest.mark.parametrize("case", [SMALL_CASES[2], SMALL_CASES[4], MESH_CASES[0], MESH_CASES[1]], ids=case_id)
+def test_culling_is_bit_neutral(case, pkg, prod):
+    """t-range box culling (not in the reference) vs the faithful traversal: same bits, same rays."""
+    name, kw, aa = case
+    wp, cp = scenes.CONFIGS[name](prod, **kw)
+    ds = pkg.DeviceScene(pkg.FlatScene(wp))
+    a, sa = ds.render(cp, aa=aa, faithful=True)
+    b, sb = ds.render(cp, aa=aa, faithful=False)
+    assert np.array_equal(a, b)
+    assert sa.rays == sb.rays
+    ds.close()
+
+
+def test_reference_known_answers_through_cabi(pkg, prod):
+    """world.rs:186-234,249-274 and camera.rs:328-337 through rtc_trace_rays / rtc_is_shadowed."""
+    w, c = scenes.default_world(prod)
+    ds = pkg.DeviceScene(pkg.FlatScene(w))
+    rgb, t = ds.trace_rays([[0, 0, -5], [0, 0, -5]], [[0, 0, 1], [0, 1, 0]])
+    assert abs(t[0] - 4.0) < 1e-5 and t[1] == -1.0
+    assert np.allclose(rgb[0], [0.38066, 0.47583, 0.2855], atol=1e-5) and np.all(rgb[1] == 0)
+    assert ds.is_shadowed([0, 10, 0]) is False
+    assert ds.is_shadowed([10, -10, 10]) is True
+    assert ds.is_shadowed([-20, 20, -20]) is False
+    assert ds.is_shadowed([-2, 2, -2]) is False
+    canvas, _ = ds.render(c)
+    assert np.allclose(canvas[5, 5], [0.38066, 0.47583, 0.2855], atol=1e-5)
+    ds.close()
+
+
+def test_n1_n2_table_through_cabi(pkg, prod, orc):
+    """intersection.rs:298-335: three nested glass spheres; n1/n2 at each of the six crossings, by
+    probing from just before each crossing."""
+    def build(api):
+        T = pkg.transform
+        w = api.world()
+        w.add_light((-10, 10, -10), (1, 1, 1))
+        w.add_object(api.sphere().set_transform(T.scaling(2, 2, 2)).set_material(pkg.Material(transparency=1.0, refractive_index=1.5)))
+        w.add_object(api.sphere().set_transform(T.translation(0, 0, -0.25)).set_material(pkg.Material(transparency=1.0, refractive_index=2.0)))
+        w.add_object(api.sphere().set_transform(T.translation(0, 0, 0.25)).set_material(pkg.Material(transparency=1.0, refractive_index=2.5)))
+        return w
+    ds = pkg.DeviceScene(pkg.FlatScene(build(prod)))
+    wo = build(orc.api)
+    expected = [(1.0, 1.5), (1.5, 2.0), (2.0, 2.5), (2.5, 2.5), (2.5, 1.5), (1.5, 1.0)]
+    crossings = [2.0, 2.75, 3.25, 4.75, 5.25, 6.0]
+    for tc, (n1, n2) in zip(crossings, expected):
+        o = [0, 0, -4 + tc - 0.1]
+        got = ds.probe_hit(o, [0, 0, 1])
+        want = orc.probe_hit(wo, o, [0, 0, 1])
+        assert got[0] == 1.0 and abs(got[1] - 0.1) < 1e-9
+        assert (got[17], got[18]) == (n1, n2), (tc, got[17], got[18])
+        assert np.array_equal(got, want)
+    ds.close()
+
+
+def test_random_ray_batch_matches_oracle(pkg, prod, orc):
+    """Seeded random rays through World::color_at on the CSG/primitive scene: colours and hit t."""
+    wp, _ = scenes.primitives_csg(prod, 16, 9)
+    wo, _ = scenes.primitives_csg(orc.api, 16, 9)
+    rng = np.random.default_rng(20261104)
+    n = 4000
+    o = rng.uniform(-3, 3, size=(n, 3)) + np.array([0, 2.0, -2.0])
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    ds = pkg.DeviceScene(pkg.FlatScene(wp))
+    rgb, t = ds.trace_rays(o, d)
+    rgb0, t0 = orc.trace_rays(wo, o, d)
+    assert np.array_equal(t, t0)
+    assert np.max(np.abs(rgb - rgb0)) <= EXPECT_LIN
+    ds.close()
+
+
+def test_row_range_and_cyclic_tiles(pkg, prod):
+    """rtc_opts row ranges and rank/nranks tile ownership partition the frame exactly."""
+    wp, cp = scenes.reflect_refract(prod, 64, 40)
+    ds = pkg.DeviceScene(pkg.FlatScene(wp))
+    full, sf = ds.render(cp)
+    part = np.full_like(full, -7.0)
+    ds.render(cp, out=part, rows=(8, 24))
+    assert np.array_equal(part[8:24], full[8:24]) and np.all(part[:8] == -7.0) and np.all(part[24:] == -7.0)
+    acc = np.full_like(full, -7.0)
+    rays = 0
+    for r in range(3):
+        _, s = ds.render(cp, out=acc, tile_rows=4, rank=r, nranks=3)
+        rays += s.rays
+    assert np.array_equal(acc, full) and rays == sf.rays
+    ds.close()
+
+
+def test_empty_world_and_no_lights(pkg, prod):
+    w = prod.world()
+    c = prod.camera(8, 4, 1.0)
+    got, st, _ = pkg.render(c, w)
+    assert np.all(got == 0.0) and st.rays == 32
+    w.add_object(prod.sphere())
+    c.set_transform(pkg.transform.view_transform((0, 0, -5), (0, 0, 0), (0, 1, 0)))
+    got, st, _ = pkg.render(c, w)   # objects but no lights: surface = Σ over zero lights = black
+    assert np.all(got == 0.0) and st.rays_shadow == 0
+
+
+def test_device_quantize_kernel(pkg):
+    import torch
+    vals = np.array([-0.5, 0.0, 0.5, 1.0, 1.5, 0.0019607, 0.998, float("nan"), float("inf"), -float("inf"), 0.5 / 255, 1.5 / 255, 2.5 / 255])
+    x = torch.tensor(vals, dtype=torch.float64, device="cuda")
+    y = torch.zeros(len(vals), dtype=torch.uint8, device="cuda")
+    assert pkg.cuda_lib().rtc_quantize_device(0, x.data_ptr(), len(vals), y.data_ptr(), None) == 0
+    torch.cuda.synchronize()
+    assert np.array_equal(y.cpu().numpy(), pkg.quantize(vals))
+    assert list(y.cpu().numpy()[:5]) == [0, 0, 128, 255, 255]   # ppm.rs:105-124
