@@ -21,7 +21,8 @@ from .api import (CSG, DIFFERENCE, INTERSECTION, UNION, Material, Pattern, Scene
                   checkers_pattern, gradient_pattern, ring_pattern, stripe_pattern)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-CUDA_LIB = os.path.join(_HERE, "csrc", "librtc_cuda.so")
+# RTC_CUDA_LIB: kernel-variant experiments only (same ABI, different build flags)
+CUDA_LIB = os.environ.get("RTC_CUDA_LIB") or os.path.join(_HERE, "csrc", "librtc_cuda.so")
 HOST_LIB = os.path.join(_HERE, "host", "librth_host.so")
 
 RTC_OPT_FAITHFUL_TRAVERSAL = 1

@@ -7,6 +7,10 @@
 
 #include "rt_shade.cuh"
 
+#ifndef RTK_MIN_BLOCKS
+#define RTK_MIN_BLOCKS 3
+#endif
+
 namespace rtk {
 
 struct RenderParams {
@@ -40,7 +44,7 @@ __device__ __forceinline__ void flush_counters(const RayCounters& rc, uint32_t e
 }
 
 template <bool HAS_CSG, bool FAITHFUL>
-__global__ void __launch_bounds__(128) render_kernel(SceneView S, CameraD cam, RenderParams P, double* __restrict__ out,
+__global__ void __launch_bounds__(128, RTK_MIN_BLOCKS) render_kernel(SceneView S, CameraD cam, RenderParams P, double* __restrict__ out,
                                                      unsigned long long* __restrict__ counters) {
   // 16x8 tile per CTA; warp w → 8x4 patch (w&1, w>>1); lane → (lane&7, lane>>3)
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
