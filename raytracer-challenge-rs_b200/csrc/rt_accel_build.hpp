@@ -1,0 +1,313 @@
+// rt_accel_build.hpp — HOST-side construction of the traversal accelerator from a flattened world
+// (rtc_scene_desc). Pure C++ (no CUDA), used by rtc_scene_create and by the CPU-only test build of
+// the kernel source.
+//
+// The reference intersects a ray with EVERY top-level object (world.rs:31-38) and prunes only with
+// the boxes of its own Group tree (group.rs:49-58), whose quality collapses for rotated meshes
+// (the AABB of every re-parented child is re-derived from its AABB, geometry/mod.rs:74-85, so
+// Group::divide stops separating anything after a few levels). The accelerator keeps the
+// reference's RESULT and replaces its SEARCH:
+//   * prims    every leaf that is not inside a CSG, and every outermost CSG node (evaluated by the
+//              in-order subtree walk, because its filter needs the reference's order);
+//   * always   prims that are tested for every ray: unbounded ones (planes, open cylinders/cones),
+//              kinds whose reference intersector can report points off the exact surface (cube,
+//              cylinder, cone: EPSILON-parallel slabs, cone.rs:106) and CSGs;
+//   * bvh      a binned-SAH binary BVH over the remaining prims (triangles, spheres) with our own
+//              tight world-space boxes, traversed front to back with t-range culling;
+//   * parent   for every node the innermost enclosing reference Group, so that a candidate hit is
+//              accepted only if the ray passes BoundingBox::intersects of every enclosing Group —
+//              exactly the condition under which the reference would have reached that leaf.
+// Ties in t resolve to the lower pre-order node index (= first in the reference's traversal order).
+#pragma once
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <limits>
+#include <vector>
+
+#include "../../include/rtc.h"
+
+namespace rtk {
+
+struct BvhNode {     // 128 bytes: both children's boxes in one fetch
+  double lo0[3], hi0[3];
+  double lo1[3], hi1[3];
+  int32_t c0, n0;    // n > 0: leaf, prims [c, c+n) of bvh_prims; n == 0: inner node index c; n < 0: empty
+  int32_t c1, n1;
+  int32_t _pad[4];
+};
+
+struct AccelBuild {
+  std::vector<int32_t> parent;     // per node: innermost enclosing Group node (outside CSGs), or -1
+  std::vector<int32_t> always;     // node indices, ascending
+  std::vector<int32_t> bvh_prims;  // node indices in BVH leaf order
+  std::vector<BvhNode> bvh;        // node 0 = root (empty vector: no BVH)
+  int32_t max_depth = 0;
+};
+
+namespace accel_detail {
+
+struct Box {
+  double lo[3], hi[3];
+  void reset() {
+    for (int a = 0; a < 3; a++) { lo[a] = std::numeric_limits<double>::infinity(); hi[a] = -lo[a]; }
+  }
+  void add(const double p[3]) {
+    for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], p[a]); hi[a] = std::max(hi[a], p[a]); }
+  }
+  void add(const Box& b) {
+    for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], b.lo[a]); hi[a] = std::max(hi[a], b.hi[a]); }
+  }
+  bool finite() const {
+    for (int a = 0; a < 3; a++)
+      if (!std::isfinite(lo[a]) || !std::isfinite(hi[a]) || lo[a] > hi[a]) return false;
+    return true;
+  }
+  double area() const {
+    double dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+    return 2.0 * (dx * dy + dy * dz + dz * dx);
+  }
+};
+
+// Forward 3x4 affine from the stored inverse (rows 0..2). Returns false if singular/non-finite.
+inline bool invert_affine(const double* inv, double fwd[12]) {
+  const double a = inv[0], b = inv[1], c = inv[2], d = inv[4], e = inv[5], f = inv[6], g = inv[8], h = inv[9], i = inv[10];
+  const double det = a * (e * i - f * h) - b * (d * i - f * g) + c * (d * h - e * g);
+  if (!(std::fabs(det) > 0.0) || !std::isfinite(det)) return false;
+  const double r = 1.0 / det;
+  double m[9] = {(e * i - f * h) * r, (c * h - b * i) * r, (b * f - c * e) * r,
+                 (f * g - d * i) * r, (a * i - c * g) * r, (c * d - a * f) * r,
+                 (d * h - e * g) * r, (b * g - a * h) * r, (a * e - b * d) * r};
+  for (int row = 0; row < 3; row++) {
+    for (int col = 0; col < 3; col++) fwd[4 * row + col] = m[3 * row + col];
+    fwd[4 * row + 3] = -(m[3 * row] * inv[3] + m[3 * row + 1] * inv[7] + m[3 * row + 2] * inv[11]);
+  }
+  for (int k = 0; k < 12; k++)
+    if (!std::isfinite(fwd[k])) return false;
+  return true;
+}
+
+inline void xf(const double* m, const double p[3], double out[3]) {
+  for (int r = 0; r < 3; r++) out[r] = m[4 * r] * p[0] + m[4 * r + 1] * p[1] + m[4 * r + 2] * p[2] + m[4 * r + 3];
+}
+
+// Our own world-space bound of a BVH-eligible leaf (triangle, smooth triangle, sphere).
+inline bool leaf_world_box(const rtc_scene_desc* d, const rtc_node& nd, Box& out) {
+  double fwd[12];
+  if (!invert_affine(d->xforms + 12 * (size_t)nd.xform, fwd)) return false;
+  out.reset();
+  double w[3];
+  if (nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE) {
+    const double* g = d->tri_p1e1e2 + 9 * (size_t)nd.aux;
+    double p1[3] = {g[0], g[1], g[2]}, p2[3] = {g[0] + g[3], g[1] + g[4], g[2] + g[5]},
+           p3[3] = {g[0] + g[6], g[1] + g[7], g[2] + g[8]};
+    xf(fwd, p1, w); out.add(w);
+    xf(fwd, p2, w); out.add(w);
+    xf(fwd, p3, w); out.add(w);
+  } else if (nd.kind == RTC_SPHERE) {
+    for (int k = 0; k < 8; k++) {
+      double p[3] = {(k & 1) ? 1.0 : -1.0, (k & 2) ? 1.0 : -1.0, (k & 4) ? 1.0 : -1.0};
+      xf(fwd, p, w); out.add(w);
+    }
+  } else {
+    return false;
+  }
+  if (!out.finite()) return false;
+  // guard band: the reference's t comes from object-space arithmetic; 1e-7 relative dwarfs its rounding
+  for (int a = 0; a < 3; a++) {
+    double pad = 1e-7 * (1.0 + std::max(std::fabs(out.lo[a]), std::fabs(out.hi[a])) + (out.hi[a] - out.lo[a]));
+    out.lo[a] -= pad;
+    out.hi[a] += pad;
+  }
+  return out.finite();
+}
+
+}  // namespace accel_detail
+
+namespace accel_detail {
+
+struct Prim {
+  Box box;
+  double c[3];
+  int32_t node;
+};
+
+constexpr int SAH_BINS = 16;
+constexpr int LEAF_MAX = 4;
+
+struct Builder {
+  std::vector<Prim>& prims;
+  AccelBuild& out;
+  explicit Builder(std::vector<Prim>& p, AccelBuild& o) : prims(p), out(o) {}
+
+  // Split prims[b,e) — returns mid (b < mid < e), or -1 to make a leaf.
+  int split(int b, int e, const Box& bounds, int depth) {
+    const int n = e - b;
+    if (n <= LEAF_MAX) return -1;
+    if (depth >= 40) {  // bound the traversal stack: median split along the widest axis from here on
+      int a = 0;
+      for (int k = 1; k < 3; k++)
+        if (bounds.hi[k] - bounds.lo[k] > bounds.hi[a] - bounds.lo[a]) a = k;
+      std::nth_element(prims.begin() + b, prims.begin() + b + n / 2, prims.begin() + e,
+                       [a](const Prim& x, const Prim& y) { return x.c[a] < y.c[a]; });
+      return b + n / 2;
+    }
+    Box cb;
+    cb.reset();
+    for (int k = b; k < e; k++) cb.add(prims[(size_t)k].c);
+    int best_axis = -1, best_bin = -1;
+    double best_cost = std::numeric_limits<double>::infinity();
+    for (int a = 0; a < 3; a++) {
+      const double ext = cb.hi[a] - cb.lo[a];
+      if (!(ext > 0.0)) continue;
+      Box bb[SAH_BINS];
+      int cnt[SAH_BINS] = {0};
+      for (auto& x : bb) x.reset();
+      const double scale = SAH_BINS / ext;
+      for (int k = b; k < e; k++) {
+        int bi = (int)((prims[(size_t)k].c[a] - cb.lo[a]) * scale);
+        bi = bi < 0 ? 0 : (bi >= SAH_BINS ? SAH_BINS - 1 : bi);
+        bb[bi].add(prims[(size_t)k].box);
+        cnt[bi]++;
+      }
+      double right_area[SAH_BINS];
+      int right_cnt[SAH_BINS];
+      Box acc;
+      acc.reset();
+      int c = 0;
+      for (int k = SAH_BINS - 1; k > 0; k--) {
+        if (cnt[k]) acc.add(bb[k]);
+        c += cnt[k];
+        right_area[k] = c ? acc.area() : 0.0;
+        right_cnt[k] = c;
+      }
+      acc.reset();
+      c = 0;
+      for (int k = 0; k + 1 < SAH_BINS; k++) {
+        if (cnt[k]) acc.add(bb[k]);
+        c += cnt[k];
+        if (c == 0 || right_cnt[k + 1] == 0) continue;
+        double cost = acc.area() * c + right_area[k + 1] * right_cnt[k + 1];
+        if (cost < best_cost) { best_cost = cost; best_axis = a; best_bin = k; }
+      }
+    }
+    int mid;
+    if (best_axis < 0) {  // all centroids coincide: split in the middle
+      mid = b + n / 2;
+    } else {
+      (void)bounds;
+      const double ext = cb.hi[best_axis] - cb.lo[best_axis];
+      const double scale = SAH_BINS / ext, lo = cb.lo[best_axis];
+      const int a = best_axis, bin = best_bin;
+      auto it = std::partition(prims.begin() + b, prims.begin() + e, [&](const Prim& p) {
+        int bi = (int)((p.c[a] - lo) * scale);
+        bi = bi < 0 ? 0 : (bi >= SAH_BINS ? SAH_BINS - 1 : bi);
+        return bi <= bin;
+      });
+      mid = (int)(it - prims.begin());
+      if (mid == b || mid == e) mid = b + n / 2;
+    }
+    return mid;
+  }
+
+  static Box range_box(const std::vector<Prim>& p, int b, int e) {
+    Box r;
+    r.reset();
+    for (int k = b; k < e; k++) r.add(p[(size_t)k].box);
+    return r;
+  }
+
+  void set_child(BvhNode& nd, int which, const Box& bx, int32_t c, int32_t n) {
+    double* lo = which ? nd.lo1 : nd.lo0;
+    double* hi = which ? nd.hi1 : nd.hi0;
+    for (int a = 0; a < 3; a++) { lo[a] = bx.lo[a]; hi[a] = bx.hi[a]; }
+    if (which) { nd.c1 = c; nd.n1 = n; } else { nd.c0 = c; nd.n0 = n; }
+  }
+
+  void build() {
+    const int n = (int)prims.size();
+    out.bvh.clear();
+    out.max_depth = 0;
+    if (n == 0) return;
+    struct Task { int b, e, node, which, depth; };
+    std::vector<Task> stack;
+    BvhNode root{};
+    Box empty;
+    empty.reset();
+    set_child(root, 0, empty, 0, -1);
+    set_child(root, 1, empty, 0, -1);
+    out.bvh.push_back(root);
+    stack.push_back({0, n, 0, 0, 1});
+    while (!stack.empty()) {
+      Task t = stack.back();
+      stack.pop_back();
+      out.max_depth = std::max(out.max_depth, (int32_t)t.depth);
+      Box bx = range_box(prims, t.b, t.e);
+      int mid = split(t.b, t.e, bx, t.depth);
+      if (mid < 0) {
+        std::sort(prims.begin() + t.b, prims.begin() + t.e, [](const Prim& x, const Prim& y) { return x.node < y.node; });
+        set_child(out.bvh[(size_t)t.node], t.which, bx, t.b, t.e - t.b);
+      } else {
+        int32_t id = (int32_t)out.bvh.size();
+        BvhNode nd{};
+        set_child(nd, 0, empty, 0, -1);
+        set_child(nd, 1, empty, 0, -1);
+        out.bvh.push_back(nd);
+        set_child(out.bvh[(size_t)t.node], t.which, bx, id, 0);
+        stack.push_back({t.b, mid, id, 0, t.depth + 1});
+        stack.push_back({mid, t.e, id, 1, t.depth + 1});
+      }
+    }
+    out.bvh_prims.resize((size_t)n);
+    for (int k = 0; k < n; k++) out.bvh_prims[(size_t)k] = prims[(size_t)k].node;
+  }
+};
+
+}  // namespace accel_detail
+
+constexpr int BVH_MIN_PRIMS = 8;  // fewer BVH-eligible prims than this: test them all, no BVH
+
+// `d` must already be structurally valid (rtc_api.cu validate()).
+inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
+  using namespace accel_detail;
+  const int32_t n = (int32_t)d->n_nodes;
+  A.parent.assign((size_t)n, -1);
+  A.always.clear();
+  A.bvh_prims.clear();
+  A.bvh.clear();
+  std::vector<Prim> cand;
+  struct Open { int32_t end, node; };
+  std::vector<Open> groups;
+  int32_t i = 0;
+  while (i < n) {
+    while (!groups.empty() && groups.back().end <= i) groups.pop_back();
+    const rtc_node& nd = d->nodes[i];
+    A.parent[(size_t)i] = groups.empty() ? -1 : groups.back().node;
+    if (nd.kind == RTC_GROUP) {
+      if (nd.skip > i + 1) groups.push_back({nd.skip, i});
+      i = i + 1;
+    } else if (nd.kind == RTC_CSG) {
+      A.always.push_back(i);
+      i = nd.skip;  // the subtree is evaluated by the in-order walk
+    } else {
+      Prim p;
+      p.node = i;
+      if ((nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE || nd.kind == RTC_SPHERE) && leaf_world_box(d, nd, p.box)) {
+        for (int a = 0; a < 3; a++) p.c[a] = 0.5 * (p.box.lo[a] + p.box.hi[a]);
+        cand.push_back(p);
+      } else {
+        A.always.push_back(i);
+      }
+      i = i + 1;
+    }
+  }
+  if ((int)cand.size() < BVH_MIN_PRIMS) {
+    for (auto& p : cand) A.always.push_back(p.node);
+    std::sort(A.always.begin(), A.always.end());
+    return;
+  }
+  Builder b(cand, A);
+  b.build();
+}
+
+}  // namespace rtk

@@ -8,6 +8,7 @@
 #pragma once
 #include "../../include/rtc.h"
 #include "rt_math.cuh"
+#include "rt_accel_build.hpp"
 
 namespace rtk {
 
@@ -23,9 +24,16 @@ struct SceneView {
   const rtc_pattern* patterns;
   const rtc_light* lights;
   const int32_t* csg_parent; // per node: nearest enclosing CSG node, or -1
+  // traversal accelerator (rt_accel_build.hpp)
+  const int32_t* parent;     // per node: innermost enclosing reference Group (outside CSGs), or -1
+  const int32_t* always;     // prims tested for every ray (node indices, ascending)
+  const int32_t* bvh_prims;  // node indices in BVH leaf order
+  const BvhNode* bvh;        // binary BVH, node 0 = root
   int32_t n_nodes;
   int32_t n_lights;
   int32_t has_csg;
+  int32_t n_always;
+  int32_t n_bvh;             // BVH node count (0: no BVH)
   int32_t _pad;
 };
 
@@ -170,9 +178,22 @@ RTC_HD bool isect_triangle(const RayD& r, const double* g, double& t, double& u,
   return true;
 }
 
+// Up to 4 intersections of one leaf, in the order the reference pushes them (cylinder/cone: two
+// walls + two caps is the maximum).
+struct LeafHits {
+  double t0, t1, t2, t3;
+  int n;
+  RTC_HD void push(double t) {
+    if (n == 0) t0 = t; else if (n == 1) t1 = t; else if (n == 2) t2 = t; else t3 = t;
+    n++;
+  }
+};
+
 // Dispatch on the leaf kind. `nd` is the node (already loaded), `lr` the object-space ray.
-template <class Emit>
-RTC_HD void isect_leaf(const SceneView& S, const rtc_node& nd, const RayD& lr, Emit&& emit) {
+RTC_HD void isect_leaf(const SceneView& S, const rtc_node& nd, const RayD& lr, LeafHits& h) {
+  h.n = 0;
+  h.t0 = h.t1 = h.t2 = h.t3 = 0.0;
+  auto emit = [&](double t) { h.push(t); };
   switch (nd.kind) {
     case RTC_SPHERE: isect_sphere(lr, emit); break;
     case RTC_PLANE: isect_plane(lr, emit); break;
@@ -190,7 +211,7 @@ RTC_HD void isect_leaf(const SceneView& S, const rtc_node& nd, const RayD& lr, E
     case RTC_TRIANGLE:
     case RTC_SMOOTH_TRIANGLE: {
       double t, u, v;
-      if (isect_triangle(lr, S.tri_geom + 9 * (size_t)nd.aux, t, u, v)) emit(t);
+      if (isect_triangle(lr, S.tri_geom + 9 * (size_t)nd.aux, t, u, v)) h.push(t);
       break;
     }
     default: break;

@@ -19,6 +19,7 @@ struct RenderParams {
   uint32_t owned_rows;          // rows of the launch domain (owned tiles * tile_rows)
   uint32_t aa, average;
   int32_t max_depth;
+  uint32_t faithful;             // RTC_OPT_FAITHFUL_TRAVERSAL: the reference's own search order
 };
 
 // counters[0..3] rays primary/shadow/reflect/refract, [4] overflow pixels, [5] NaN pixels
@@ -43,7 +44,7 @@ __device__ __forceinline__ void flush_counters(const RayCounters& rc, uint32_t e
   }
 }
 
-template <bool HAS_CSG, bool FAITHFUL>
+template <bool HAS_CSG>
 __global__ void __launch_bounds__(128, RTK_MIN_BLOCKS) render_kernel(SceneView S, CameraD cam, RenderParams P, double* __restrict__ out,
                                                      unsigned long long* __restrict__ counters) {
   // 16x8 tile per CTA; warp w → 8x4 patch (w&1, w>>1); lane → (lane&7, lane>>3)
@@ -59,7 +60,7 @@ __global__ void __launch_bounds__(128, RTK_MIN_BLOCKS) render_kernel(SceneView S
   Scratch<HAS_CSG> scratch;
   RayCounters rc = {0u, 0u, 0u, 0u};
   uint32_t err = 0;
-  V3 c = render_pixel<HAS_CSG, FAITHFUL>(S, cam, px, py, P.aa, P.average != 0, P.max_depth, scratch, rc, &err);
+  V3 c = render_pixel<HAS_CSG>(S, cam, px, py, P.aa, P.average != 0, P.max_depth, P.faithful != 0, scratch, rc, &err);
   double* o = out + ((size_t)py * cam.hsize + px) * 3;  // Canvas::pixel_idx, canvas.rs:44-48
   o[0] = c.x;
   o[1] = c.y;
@@ -68,7 +69,7 @@ __global__ void __launch_bounds__(128, RTK_MIN_BLOCKS) render_kernel(SceneView S
 }
 
 // World::color_at for a batch of rays (debug / known-answer entry)
-template <bool HAS_CSG, bool FAITHFUL>
+template <bool HAS_CSG>
 __global__ void __launch_bounds__(128) trace_kernel(SceneView S, size_t n, const double* __restrict__ origins,
                                                     const double* __restrict__ dirs, int remaining,
                                                     double* __restrict__ rgb, double* __restrict__ t_out,
@@ -83,7 +84,7 @@ __global__ void __launch_bounds__(128) trace_kernel(SceneView S, size_t n, const
   r.d = v3(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]);
   double t = -1.0;
   rc.primary++;
-  V3 c = color_at<HAS_CSG, FAITHFUL>(S, r, remaining, scratch, rc, &err, &t);
+  V3 c = color_at<HAS_CSG>(S, r, remaining, true, scratch, rc, &err, &t);
   if (rgb) { rgb[3 * i] = c.x; rgb[3 * i + 1] = c.y; rgb[3 * i + 2] = c.z; }
   if (t_out) t_out[i] = t;
   flush_counters(rc, err, counters);
@@ -96,17 +97,17 @@ __global__ void probe_kernel(SceneView S, RayD ray, double* __restrict__ out, un
   Scratch<HAS_CSG> scratch;
   uint32_t err = 0;
   for (int i = 0; i < 20; i++) out[i] = 0.0;
-  ClosestHit ch;
-  ch.init();
-  walk_scene<HAS_CSG, true>(S, ray, ch, scratch.csg(), &err);
-  if (ch.best_node >= 0) {
-    rtc_node nd = load_node(S.nodes + ch.best_node);
+  Query ch;
+  ch.init_closest(&err);
+  search<HAS_CSG>(S, ray, ch, scratch.csg(), &scratch.bvh, true, &err);
+  if (ch.node >= 0) {
+    rtc_node nd = load_node(S.nodes + ch.node);
     Comps c;
-    prepare(S, ray, ch.best_t, ch.best_node, nd, c);
-    NegCollect nc;
-    nc.init(&scratch.neg, &err);
-    walk_scene<HAS_CSG, true>(S, ray, nc, scratch.csg(), &err);
-    containers_n1n2(S, scratch.neg, ch.best_node, c.n1, c.n2, &err);
+    prepare(S, ray, ch.limit, ch.node, nd, c);
+    Query nc;
+    nc.init_neg(&scratch.neg, &err);
+    search<HAS_CSG>(S, ray, nc, scratch.csg(), &scratch.bvh, true, &err);
+    containers_n1n2(S, scratch.neg, ch.node, c.n1, c.n2, &err);
     out[0] = 1.0; out[1] = c.t;
     out[2] = c.point.x; out[3] = c.point.y; out[4] = c.point.z;
     out[5] = c.normalv.x; out[6] = c.normalv.y; out[7] = c.normalv.z;
@@ -127,7 +128,14 @@ __global__ void shadow_kernel(SceneView S, V3 point, int light, int* __restrict_
   uint32_t err = 0;
   const rtc_light* L = S.lights + light;
   V3 lp = v3(L->position[0], L->position[1], L->position[2]);
-  out[0] = is_shadowed<HAS_CSG, true>(S, point, lp, scratch.csg(), &err) ? 1 : 0;
+  V3 v = lp - point;  // World::is_shadowed, world.rs:95-105
+  RayD r;
+  r.o = point;
+  r.d = normalize(v);
+  Query sh;
+  sh.init_shadow(magnitude(v), &err);
+  search<HAS_CSG>(S, r, sh, scratch.csg(), &scratch.bvh, true, &err);
+  out[0] = sh.done() ? 1 : 0;
   RayCounters rc = {0u, 0u, 0u, 0u};
   flush_counters(rc, err, counters);
 }

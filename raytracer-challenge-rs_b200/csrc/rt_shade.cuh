@@ -7,7 +7,7 @@
 // schlick), geometry/mod.rs:51-56 (normal_at), material.rs:38-82 (lighting), pattern/*.rs,
 // camera.rs:57-126 (ray_for_pixel, rays_for_pixel, get_offsets), color.rs:26-33 (average).
 #pragma once
-#include "rt_walk.cuh"
+#include "rt_accel.cuh"
 
 namespace rtk {
 
@@ -30,11 +30,13 @@ struct Scratch;
 template <>
 struct Scratch<false> {
   HitList neg;
+  BvhStack bvh;
   RTC_HD CsgScratch* csg() { return nullptr; }
 };
 template <>
 struct Scratch<true> {
   HitList neg;
+  BvhStack bvh;
   CsgScratch cs;
   RTC_HD CsgScratch* csg() { return &cs; }
 };
@@ -230,20 +232,6 @@ RTC_HD double schlick(const Comps& c) {
   return r0 + (1.0 - r0) * (x * x4);
 }
 
-// World::is_shadowed (world.rs:95-105)
-template <bool HAS_CSG, bool FAITHFUL>
-RTC_HD bool is_shadowed(const SceneView& S, V3 point, V3 light_pos, CsgScratch* cs, uint32_t* err) {
-  V3 v = light_pos - point;
-  double distance = magnitude(v);
-  RayD r;
-  r.o = point;
-  r.d = normalize(v);
-  ShadowHit sh;
-  sh.init(distance);
-  walk_scene<HAS_CSG, FAITHFUL>(S, r, sh, cs, err);
-  return sh.found;
-}
-
 struct Frame {
   V3 surface;      // Σ lights
   V3 reflected;    // reflected_color result
@@ -253,99 +241,144 @@ struct Frame {
   uint8_t need_refract, use_schlick, _pad;
 };
 
-// World::color_at(ray, remaining = max_depth) (world.rs:70-81), iteratively.
-template <bool HAS_CSG, bool FAITHFUL>
-RTC_HD V3 color_at(const SceneView& S, RayD ray, int max_depth, Scratch<HAS_CSG>& scratch, RayCounters& rc,
-                   uint32_t* err, double* t_out = nullptr) {
+RTC_HD V3 combine(const Frame& f, V3 refracted) {  // world.rs:62-67
+  return f.use_schlick ? f.surface + f.reflected * f.reflectance + refracted * (1.0 - f.reflectance)
+                       : f.surface + f.reflected + refracted;
+}
+
+// World::color_at(ray, remaining = max_depth) (world.rs:70-81) with shade_hit, is_shadowed,
+// reflected_color and refracted_color (world.rs:40-134) as ONE state machine around ONE search
+// site: every closest-hit, shadow (world.rs:95-105) and containers query of the whole recursion
+// tree is put to the same search, in the reference's evaluation order. The caller loops
+//     tr.start(ray, depth);  for (;;) { search(S, tr.qray, tr.q, ...);  if (tr.advance(S, ...)) break; }
+// so that a persistent kernel can keep every lane of a warp at that one search site, whatever
+// pixel, recursion depth or phase each lane is in.
+enum : int { PH_CLOSEST = 0, PH_SHADOW = 1, PH_NEG = 2 };
+enum : int { NX_RETURN = 0, NX_SHADOW = 1, NX_LIT = 2, NX_N1N2 = 3 };
+
+struct Tracer {
   Frame frames[MAX_FRAMES];
-  int sp = 0;                 // current frame index == depth of the ray being evaluated
-  int remaining = max_depth;
-  V3 result = v3(0.0, 0.0, 0.0);
-  CsgScratch* cs = scratch.csg();
-  for (;;) {
-    // ---- evaluate color_at(ray, remaining) up to the point where it needs a child --------------
-    bool need_child = false;
-    {
-      ClosestHit ch;
-      ch.init();
-      walk_scene<HAS_CSG, FAITHFUL>(S, ray, ch, cs, err);
-      if (t_out && sp == 0) *t_out = ch.best_node >= 0 ? ch.best_t : -1.0;
-      if (ch.best_node < 0) {
+  RayD ray;        // the ray color_at is being evaluated for (current recursion level)
+  RayD qray;       // the ray of the pending query
+  Query q;
+  Comps c;         // the hit being shaded (live across its shadow / containers queries)
+  MatD m;
+  V3 color, surface, result;
+  double t_primary;
+  int sp, remaining, li, phase;
+  bool want_reflect, want_refract;
+
+  RTC_HD void start(const RayD& r, int max_depth, uint32_t* err) {
+    ray = r;
+    qray = r;
+    sp = 0;
+    remaining = max_depth;
+    li = 0;
+    phase = PH_CLOSEST;
+    want_reflect = want_refract = false;
+    result = v3(0.0, 0.0, 0.0);
+    t_primary = -1.0;
+    c.node = -1;
+    q.init_closest(err);
+  }
+
+  // Consume the answer of the pending query; set up the next one. Returns true when color_at of the
+  // primary ray is complete (`result`).
+  RTC_HD bool advance(const SceneView& S, HitList& neg, RayCounters& rc, uint32_t* err) {
+    int next;
+    if (phase == PH_CLOSEST) {
+      if (sp == 0) t_primary = q.node >= 0 ? q.limit : -1.0;
+      if (q.node < 0) {
         result = v3(0.0, 0.0, 0.0);  // Color::black()
+        next = NX_RETURN;
       } else {
-        rtc_node nd = load_node(S.nodes + ch.best_node);
-        MatD m = load_material(S, nd.material);
-        Comps c;
-        prepare(S, ray, ch.best_t, ch.best_node, nd, c);
-        Frame& f = frames[sp];
-        // shade_hit: surface = Σ lighting, in light order, from (0,0,0)   (world.rs:41-58)
-        V3 surface = v3(0.0, 0.0, 0.0);
+        rtc_node nd = load_node(S.nodes + q.node);
+        m = load_material(S, nd.material);
+        prepare(S, ray, q.limit, q.node, nd, c);
         const double* leaf_inv = S.xforms + 12 * (size_t)nd.xform;
-        V3 color = m.pattern >= 0 ? pattern_color(S, m.pattern, leaf_inv, c.over_point) : m.color;
-        for (int li = 0; li < S.n_lights; li++) {
-          const rtc_light* L = S.lights + li;
-          V3 lp = v3(RTC_LDG(&L->position[0]), RTC_LDG(&L->position[1]), RTC_LDG(&L->position[2]));
-          V3 lint = v3(RTC_LDG(&L->intensity[0]), RTC_LDG(&L->intensity[1]), RTC_LDG(&L->intensity[2]));
-          rc.shadow++;
-          bool shadowed = is_shadowed<HAS_CSG, FAITHFUL>(S, c.over_point, lp, cs, err);
-          surface = surface + lighting(m, color, lp, lint, c.over_point, c.eyev, c.normalv, shadowed);
+        color = m.pattern >= 0 ? pattern_color(S, m.pattern, leaf_inv, c.over_point) : m.color;
+        surface = v3(0.0, 0.0, 0.0);  // shade_hit: Σ lighting in light order from (0,0,0), world.rs:41-58
+        li = 0;
+        next = S.n_lights > 0 ? NX_SHADOW : NX_LIT;
+      }
+    } else if (phase == PH_SHADOW) {
+      const rtc_light* L = S.lights + li;
+      V3 lp = v3(RTC_LDG(&L->position[0]), RTC_LDG(&L->position[1]), RTC_LDG(&L->position[2]));
+      V3 lint = v3(RTC_LDG(&L->intensity[0]), RTC_LDG(&L->intensity[1]), RTC_LDG(&L->intensity[2]));
+      surface = surface + lighting(m, color, lp, lint, c.over_point, c.eyev, c.normalv, q.done());
+      li++;
+      next = li < S.n_lights ? NX_SHADOW : NX_LIT;
+    } else {
+      containers_n1n2(S, neg, c.node, c.n1, c.n2, err);
+      next = NX_N1N2;
+    }
+    if (next == NX_SHADOW) {  // World::is_shadowed(over_point, light li), world.rs:95-105
+      const rtc_light* L = S.lights + li;
+      V3 lp = v3(RTC_LDG(&L->position[0]), RTC_LDG(&L->position[1]), RTC_LDG(&L->position[2]));
+      V3 v = lp - c.over_point;
+      double distance = magnitude(v);
+      qray.o = c.over_point;
+      qray.d = normalize(v);
+      q.init_shadow(distance, err);
+      rc.shadow++;
+      phase = PH_SHADOW;
+      return false;
+    }
+    bool descend = false;
+    if (next == NX_LIT) {
+      Frame& f = frames[sp];
+      f.surface = surface;
+      f.reflective = m.reflective;
+      f.transparency = m.transparency;
+      want_reflect = !(feq(m.reflective, 0.0) || remaining == 0);    // world.rs:108
+      want_refract = !(feq(m.transparency, 0.0) || remaining == 0);  // world.rs:117
+      f.use_schlick = (m.reflective > 0.0 && m.transparency > 0.0) ? 1 : 0;  // world.rs:62
+      f.need_refract = 0;
+      f.reflectance = 0.0;
+      if (want_refract || f.use_schlick) {
+        // n1/n2 are only ever consumed by refracted_color and schlick
+        qray = ray;
+        q.init_neg(&neg, err);
+        phase = PH_NEG;
+        return false;
+      }
+      next = NX_N1N2;
+    }
+    if (next == NX_N1N2) {
+      Frame& f = frames[sp];
+      if (f.use_schlick) f.reflectance = schlick(c);
+      if (want_refract) {  // world.rs:121-131
+        double n_ratio = c.n1 / c.n2;
+        double cos_i = dot(c.eyev, c.normalv);
+        double sin2_t = n_ratio * n_ratio * (1.0 - cos_i * cos_i);
+        if (!(sin2_t > 1.0)) {
+          double cos_t = sqrt(1.0 - sin2_t);
+          f.refr_ray.o = c.under_point;
+          f.refr_ray.d = c.normalv * (n_ratio * cos_i - cos_t) - c.eyev * n_ratio;  // not normalised
+          f.need_refract = 1;
         }
-        f.surface = surface;
-        f.reflective = m.reflective;
-        f.transparency = m.transparency;
-        bool want_reflect = !(feq(m.reflective, 0.0) || remaining == 0);    // world.rs:108
-        bool want_refract = !(feq(m.transparency, 0.0) || remaining == 0);  // world.rs:117
-        f.use_schlick = (m.reflective > 0.0 && m.transparency > 0.0) ? 1 : 0;  // world.rs:62
-        f.need_refract = 0;
-        f.reflectance = 0.0;
-        if (want_refract || f.use_schlick) {
-          // n1/n2 are only ever consumed by refracted_color and schlick
-          NegCollect nc;
-          nc.init(&scratch.neg, err);
-          walk_scene<HAS_CSG, FAITHFUL>(S, ray, nc, cs, err);
-          containers_n1n2(S, scratch.neg, ch.best_node, c.n1, c.n2, err);
-        }
-        if (f.use_schlick) f.reflectance = schlick(c);
-        if (want_refract) {  // world.rs:121-131
-          double n_ratio = c.n1 / c.n2;
-          double cos_i = dot(c.eyev, c.normalv);
-          double sin2_t = n_ratio * n_ratio * (1.0 - cos_i * cos_i);
-          if (!(sin2_t > 1.0)) {
-            double cos_t = sqrt(1.0 - sin2_t);
-            f.refr_ray.o = c.under_point;
-            f.refr_ray.d = c.normalv * (n_ratio * cos_i - cos_t) - c.eyev * n_ratio;  // not normalised
-            f.need_refract = 1;
-          }
-        }
-        if (want_reflect) {
-          rc.reflect++;
-          f.state = 1;
-          ray.o = c.over_point;
-          ray.d = c.reflectv;
-          need_child = true;
+      }
+      if (want_reflect) {
+        rc.reflect++;
+        f.state = 1;
+        ray.o = c.over_point;
+        ray.d = c.reflectv;
+        descend = true;
+      } else {
+        f.reflected = v3(0.0, 0.0, 0.0);
+        if (f.need_refract) {
+          rc.refract++;
+          f.state = 2;
+          ray = f.refr_ray;
+          descend = true;
         } else {
-          f.reflected = v3(0.0, 0.0, 0.0);
-          if (f.need_refract) {
-            rc.refract++;
-            f.state = 2;
-            ray = f.refr_ray;
-            need_child = true;
-          } else {
-            V3 refracted = v3(0.0, 0.0, 0.0);
-            result = f.use_schlick ? f.surface + f.reflected * f.reflectance + refracted * (1.0 - f.reflectance)
-                                   : f.surface + f.reflected + refracted;
-          }
+          result = combine(f, v3(0.0, 0.0, 0.0));
         }
       }
     }
-    if (need_child) {
-      sp++;
-      remaining--;
-      continue;
-    }
-    // ---- return `result` to the parents ---------------------------------------------------------
-    for (;;) {
-      if (sp == 0) return result;
+    // ---- return `result` to the parents -----------------------------------------------------------
+    while (!descend) {
+      if (sp == 0) return true;
       sp--;
       remaining++;
       Frame& f = frames[sp];
@@ -355,23 +388,34 @@ RTC_HD V3 color_at(const SceneView& S, RayD ray, int max_depth, Scratch<HAS_CSG>
           rc.refract++;
           f.state = 2;
           ray = f.refr_ray;
-          need_child = true;
-          break;
+          descend = true;
+        } else {
+          result = combine(f, v3(0.0, 0.0, 0.0));
         }
-        V3 refracted = v3(0.0, 0.0, 0.0);
-        result = f.use_schlick ? f.surface + f.reflected * f.reflectance + refracted * (1.0 - f.reflectance)
-                               : f.surface + f.reflected + refracted;
       } else {
-        V3 refracted = result * f.transparency;  // world.rs:133
-        result = f.use_schlick ? f.surface + f.reflected * f.reflectance + refracted * (1.0 - f.reflectance)
-                               : f.surface + f.reflected + refracted;
+        result = combine(f, result * f.transparency);  // world.rs:133
       }
     }
-    if (need_child) {
-      sp++;
-      remaining--;
-    }
+    sp++;
+    remaining--;
+    qray = ray;
+    q.init_closest(err);
+    phase = PH_CLOSEST;
+    return false;
   }
+};
+
+template <bool HAS_CSG>
+RTC_HD V3 color_at(const SceneView& S, const RayD& ray, int max_depth, bool faithful, Scratch<HAS_CSG>& scratch, RayCounters& rc,
+                   uint32_t* err, double* t_out = nullptr) {
+  Tracer tr;
+  tr.start(ray, max_depth, err);
+  for (;;) {
+    search<HAS_CSG>(S, tr.qray, tr.q, scratch.csg(), &scratch.bvh, faithful, err);
+    if (tr.advance(S, scratch.neg, rc, err)) break;
+  }
+  if (t_out) *t_out = tr.t_primary;
+  return tr.result;
 }
 
 struct CameraD {
@@ -415,19 +459,19 @@ RTC_HD void aa_offset(uint32_t aa, uint32_t s, double& ox, double& oy) {
 
 // One pixel of Camera::render (aa==1, camera.rs:133-148: colour stored as is) or of
 // render_multithreaded (camera.rs:178-187: Color::average = sequential sum * (1.0/n)).
-template <bool HAS_CSG, bool FAITHFUL>
+template <bool HAS_CSG>
 RTC_HD V3 render_pixel(const SceneView& S, const CameraD& cam, uint32_t px, uint32_t py, uint32_t aa, bool average,
-                       int max_depth, Scratch<HAS_CSG>& scratch, RayCounters& rc, uint32_t* err) {
+                       int max_depth, bool faithful, Scratch<HAS_CSG>& scratch, RayCounters& rc, uint32_t* err) {
   if (!average) {
     rc.primary++;
-    return color_at<HAS_CSG, FAITHFUL>(S, ray_for_pixel(cam, px, py, 0.5, 0.5), max_depth, scratch, rc, err);
+    return color_at<HAS_CSG>(S, ray_for_pixel(cam, px, py, 0.5, 0.5), max_depth, faithful, scratch, rc, err);
   }
   V3 avg = v3(0.0, 0.0, 0.0);
   for (uint32_t s = 0; s < aa; s++) {
     double ox, oy;
     aa_offset(aa, s, ox, oy);
     rc.primary++;
-    avg = avg + color_at<HAS_CSG, FAITHFUL>(S, ray_for_pixel(cam, px, py, ox, oy), max_depth, scratch, rc, err);
+    avg = avg + color_at<HAS_CSG>(S, ray_for_pixel(cam, px, py, ox, oy), max_depth, faithful, scratch, rc, err);
   }
   return avg * (1.0 / (double)aa);
 }

@@ -1,19 +1,20 @@
-// rt_walk.cuh — scene traversal: World::intersect (world.rs:31-38), Group::intersect
-// (group.rs:49-58) and Csg::local_intersect + filter_intersections (csg.rs:71-91,115-126) as ONE
-// stackless pre-order walk over the flattened node array (skip pointers), feeding a consumer.
+// rt_walk.cuh — the query a ray puts to the world, and the reference-order walk.
 //
 // The reference collects every intersection of every object into a Vec, sorts it by t and then
-// looks at the front; the consumers below compute the same answers from the stream:
-//   ClosestHit  — hit(): first t >= 0 of the sorted list (intersection.rs:118-120). Ties in t are
-//                 resolved like a stable sort: first in traversal order wins (strict <).
-//   ShadowHit   — shadow_hit() + `t < distance` (intersection.rs:122-125, world.rs:101-104):
-//                 any has_shadow intersection with 0 <= t < distance, early exit.
-//   NegCollect  — the sorted prefix of the list that precedes the hit, i.e. every t < 0, which is
-//                 all prepare_computations' containers loop ever looks at (intersection.rs:63-90).
-// Inside a CSG subtree intersections go to a bounded per-thread buffer which is sorted (stable) and
-// filtered when the walk leaves that CSG node — exactly the reference's per-CSG sort and filter,
-// nested CSGs included; survivors of the outermost CSG are then streamed to the consumer at the
-// CSG's position in the traversal order.
+// looks at the front (world.rs:31-38, intersection.rs:108-125). Nothing is collected here: a
+// `Query` says what the caller would read off that sorted list, and the searches stream
+// intersections into it:
+//   Q_CLOSEST  hit(): first t >= 0 of the sorted list (intersection.rs:118-120). Equal t resolves to
+//              the lower pre-order node index = the entry a stable sort of the reference's
+//              traversal-ordered list puts first.
+//   Q_SHADOW   shadow_hit() + `t < distance` (intersection.rs:122-125, world.rs:101-104): any
+//              has_shadow intersection with 0 <= t < distance; early exit.
+//   Q_NEG      the sorted prefix that precedes the hit, i.e. every t < 0 — all the containers loop
+//              of prepare_computations ever looks at (intersection.rs:63-90).
+// walk_range() is the reference's own search: depth-first, in order, over a range of the flattened
+// node array (World::intersect for the whole array, Group::intersect with its box test
+// group.rs:49-58, Csg::local_intersect + filter_intersections csg.rs:71-126 with a bounded
+// per-thread buffer that is stable-sorted and filtered when the walk leaves the CSG node).
 #pragma once
 #include "rt_isect.cuh"
 
@@ -23,6 +24,7 @@ constexpr int CSG_MAX_DEPTH = 4;    // nested CSG levels per ray
 constexpr int HIT_CAP = 64;         // bounded list capacity (CSG hit buffer, negative-t list)
 
 enum : uint32_t { ERR_OVERFLOW = 1u, ERR_NAN = 2u };
+enum : int32_t { Q_CLOSEST = 0, Q_SHADOW = 1, Q_NEG = 2 };
 
 RTC_HD rtc_node load_node(const rtc_node* p) {
 #if defined(__CUDA_ARCH__)
@@ -37,11 +39,53 @@ RTC_HD rtc_node load_node(const rtc_node* p) {
 #endif
 }
 
-// Sorted bounded list of (t, node); insertion keeps equal t in arrival order (stable).
+// Sorted bounded list of (t, node).
 struct HitList {
   double t[HIT_CAP];
   int32_t node[HIT_CAP];
   int32_t n;
+};
+
+struct Query {
+  double limit;      // Q_CLOSEST: best t so far (inf); Q_SHADOW: distance to the light
+  int32_t mode;
+  int32_t node;      // Q_CLOSEST: best node (-1); Q_SHADOW: 1 when found
+  HitList* list;     // Q_NEG
+  uint32_t* err;
+
+  RTC_HD void init_closest(uint32_t* e) { mode = Q_CLOSEST; limit = rt_inf(); node = -1; list = nullptr; err = e; }
+  RTC_HD void init_shadow(double distance, uint32_t* e) { mode = Q_SHADOW; limit = distance; node = 0; list = nullptr; err = e; }
+  RTC_HD void init_neg(HitList* l, uint32_t* e) { mode = Q_NEG; limit = 0.0; node = -1; list = l; l->n = 0; err = e; }
+
+  // would the reference's sorted list hand this intersection to the caller?
+  RTC_HD bool want(double t, int32_t nd, uint32_t flags) const {
+    if (mode == Q_CLOSEST) return t >= 0.0 && (t < limit || (t == limit && nd < node));
+    if (mode == Q_SHADOW) return t >= 0.0 && t < limit && (flags & RTC_FLAG_SHADOW);
+    return t < 0.0;
+  }
+  RTC_HD void take(double t, int32_t nd) {
+    if (mode == Q_CLOSEST) { limit = t; node = nd; return; }
+    if (mode == Q_SHADOW) { node = 1; return; }
+    int n = list->n;
+    if (n >= HIT_CAP) { *err |= ERR_OVERFLOW; return; }
+    int k = n;
+    // sorted by (t, node): the order of the reference's stable-sorted list
+    while (k > 0 && (list->t[k - 1] > t || (list->t[k - 1] == t && list->node[k - 1] > nd))) {
+      list->t[k] = list->t[k - 1];
+      list->node[k] = list->node[k - 1];
+      k--;
+    }
+    list->t[k] = t;
+    list->node[k] = nd;
+    list->n = n + 1;
+  }
+  RTC_HD void hit(double t, int32_t nd, uint32_t flags) { if (want(t, nd, flags)) take(t, nd); }
+  RTC_HD bool done() const { return mode == Q_SHADOW && node != 0; }
+  // conservative t-range culling of one of OUR boxes [tmin,tmax] (never of a reference box)
+  RTC_HD bool cull(double tmin, double tmax) const {
+    if (mode == Q_NEG) return tmin > 1e-6 * (1.0 + fabs(tmin));
+    return tmax < -1e-6 * (1.0 + fabs(tmax)) || tmin > limit + 1e-6 * (1.0 + fabs(limit));
+  }
 };
 
 // csg.rs:22-40
@@ -50,56 +94,6 @@ RTC_HD bool csg_allowed(uint32_t op, bool lhit, bool inl, bool inr) {
   if (op == RTC_CSG_INTERSECTION) return (lhit && inr) || (!lhit && inl);
   return (lhit && !inr) || (!lhit && inl);
 }
-
-struct ClosestHit {
-  double best_t;
-  int32_t best_node;
-  RTC_HD void init() { best_t = rt_inf(); best_node = -1; }
-  RTC_HD void hit(double t, int32_t node, uint32_t) {
-    if (t >= 0.0 && t < best_t) { best_t = t; best_node = node; }
-  }
-  RTC_HD bool done() const { return false; }
-  // conservative t-range culling of a group box [tmin,tmax] (not in the reference; never removes
-  // an intersection the reference would accept — see DESIGN.md "t-range culling")
-  RTC_HD bool cull(double tmin, double tmax) const {
-    return tmax < -1e-6 * (1.0 + fabs(tmax)) || tmin > best_t + 1e-6 * (1.0 + fabs(best_t));
-  }
-};
-
-struct ShadowHit {
-  double distance;
-  bool found;
-  RTC_HD void init(double d) { distance = d; found = false; }
-  RTC_HD void hit(double t, int32_t, uint32_t flags) {
-    if (t >= 0.0 && t < distance && (flags & RTC_FLAG_SHADOW)) found = true;
-  }
-  RTC_HD bool done() const { return found; }
-  RTC_HD bool cull(double tmin, double tmax) const {
-    return tmax < -1e-6 * (1.0 + fabs(tmax)) || tmin > distance + 1e-6 * (1.0 + fabs(distance));
-  }
-};
-
-struct NegCollect {
-  HitList* list;
-  uint32_t* err;
-  RTC_HD void init(HitList* l, uint32_t* e) { list = l; err = e; l->n = 0; }
-  RTC_HD void hit(double t, int32_t node, uint32_t) {
-    if (!(t < 0.0)) return;
-    int n = list->n;
-    if (n >= HIT_CAP) { *err |= ERR_OVERFLOW; return; }
-    int k = n;
-    while (k > 0 && list->t[k - 1] > t) {  // stable: stop at equal
-      list->t[k] = list->t[k - 1];
-      list->node[k] = list->node[k - 1];
-      k--;
-    }
-    list->t[k] = t;
-    list->node[k] = node;
-    list->n = n + 1;
-  }
-  RTC_HD bool done() const { return false; }
-  RTC_HD bool cull(double tmin, double) const { return tmin > 1e-6 * (1.0 + fabs(tmin)); }
-};
 
 struct CsgLevel {
   RayD saved;      // the ray outside this CSG
@@ -148,16 +142,18 @@ RTC_HD int csg_finalize(const SceneView& S, HitList& buf, int start, int32_t ci,
   return w;
 }
 
-// The walk. FAITHFUL=true visits exactly the nodes the reference visits (no t-range culling).
-template <bool HAS_CSG, bool FAITHFUL, class Consumer>
-RTC_HD void walk_scene(const SceneView& S, const RayD& world_ray, Consumer& C, CsgScratch* cs, uint32_t* err) {
+// The in-order walk over nodes [begin, end): visits exactly the nodes the reference visits
+// (World::intersect for the whole array; one CSG subtree when called by the accelerated search).
+template <bool HAS_CSG>
+RTC_HD void walk_range(const SceneView& S, const RayD& world_ray, Query& C, CsgScratch* cs, uint32_t* err,
+                       int32_t begin, int32_t end) {
   RayD cur = world_ray;
   RayD lr;               // object-space ray cache, keyed by transform id
   int32_t lr_xf = -1;
   int depth = 0;
   if (HAS_CSG) cs->buf.n = 0;
-  const int32_t n_nodes = S.n_nodes;
-  int32_t i = 0;
+  const int32_t n_nodes = end;
+  int32_t i = begin;
   for (;;) {
     if (HAS_CSG) {
       while (depth > 0 && i == cs->level[depth - 1].skip) {
@@ -182,7 +178,6 @@ RTC_HD void walk_scene(const SceneView& S, const RayD& world_ray, Consumer& C, C
     if (nd.kind == RTC_GROUP) {
       double tmin, tmax;
       bool ok = box_intersects(S.boxes + 6 * (size_t)nd.aux, cur, tmin, tmax);
-      if (ok && !FAITHFUL && (!HAS_CSG || depth == 0) && C.cull(tmin, tmax)) ok = false;
       i = ok ? i + 1 : nd.skip;
     } else if (nd.kind == RTC_CSG) {
       if (HAS_CSG) {
@@ -214,20 +209,23 @@ RTC_HD void walk_scene(const SceneView& S, const RayD& world_ray, Consumer& C, C
         lr = ray_transform(S.xforms + 12 * (size_t)nd.xform, cur);
         lr_xf = nd.xform;
       }
-      if (HAS_CSG && depth > 0) {
-        HitList& buf = cs->buf;
-        isect_leaf(S, nd, lr, [&](double t) {
+      LeafHits h;
+      isect_leaf(S, nd, lr, h);
+#if defined(__CUDACC__)
+#pragma unroll
+#endif
+      for (int k = 0; k < 4; k++) {
+        if (k < h.n) {
+          const double t = k == 0 ? h.t0 : (k == 1 ? h.t1 : (k == 2 ? h.t2 : h.t3));
           if (t != t) *err |= ERR_NAN;
-          if (buf.n >= HIT_CAP) { *err |= ERR_OVERFLOW; return; }
-          buf.t[buf.n] = t;
-          buf.node[buf.n] = i;
-          buf.n++;
-        });
-      } else {
-        isect_leaf(S, nd, lr, [&](double t) {
-          if (t != t) *err |= ERR_NAN;
-          C.hit(t, i, nd.flags);
-        });
+          if (HAS_CSG && depth > 0) {
+            HitList& buf = cs->buf;
+            if (buf.n >= HIT_CAP) { *err |= ERR_OVERFLOW; }
+            else { buf.t[buf.n] = t; buf.node[buf.n] = i; buf.n++; }
+          } else {
+            C.hit(t, i, nd.flags);
+          }
+        }
       }
       i = i + 1;
     }

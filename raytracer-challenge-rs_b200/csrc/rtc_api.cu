@@ -113,11 +113,6 @@ int validate(const rtc_scene_desc* d, std::vector<int32_t>& csg_parent, bool& ha
 
 size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
 
-template <class K>
-void launch_render(bool has_csg, bool faithful, K&& go) {
-  if (has_csg) { if (faithful) go(std::true_type{}, std::true_type{}); else go(std::true_type{}, std::false_type{}); }
-  else { if (faithful) go(std::false_type{}, std::true_type{}); else go(std::false_type{}, std::false_type{}); }
-}
 
 int read_counters(rtc_scene* s, cudaStream_t stream, rtc_stats* stats) {
   unsigned long long h[N_COUNTERS];
@@ -176,9 +171,10 @@ int launch_frame(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool f
   dim3 block(128), grid((cam.hsize + 15) / 16, (P.owned_rows + 7) / 8);
   CUDA_TRY(cudaEventRecord(s->ev0, stream));
   if (grid.x > 0 && grid.y > 0) {
-    launch_render(s->has_csg, faithful, [&](auto csg, auto fa) {
-      render_kernel<decltype(csg)::value, decltype(fa)::value><<<grid, block, 0, stream>>>(s->view, cam, P, out, s->d_counters);
-    });
+    RenderParams Pk = P;
+    Pk.faithful = faithful ? 1u : 0u;
+    if (s->has_csg) render_kernel<true><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
+    else render_kernel<false><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
     s->launches++;
   }
   CUDA_TRY(cudaEventRecord(s->ev1, stream));
@@ -208,9 +204,12 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   if (rtc_device_count() <= device || device < 0) return fail(RTC_ERR_CUDA, "no such CUDA device (this library has no CPU fallback)");
   CUDA_TRY(cudaSetDevice(device));
 
-  // one slab: [nodes | xforms | boxes | limits | tri_geom | tri_normals | materials | patterns | lights | csg_parent]
+  AccelBuild accel;
+  build_accel(d, accel);
+  // one slab: [nodes | xforms | boxes | limits | tri_geom | tri_normals | materials | patterns | lights | csg_parent
+  //            | parent | always | bvh_prims | bvh]
   struct Part { const void* src; size_t bytes; size_t off; };
-  Part parts[10] = {
+  Part parts[14] = {
       {d->nodes, sizeof(rtc_node) * d->n_nodes, 0},
       {d->xforms, sizeof(double) * 12 * d->n_xforms, 0},
       {d->boxes, sizeof(double) * 6 * d->n_boxes, 0},
@@ -220,7 +219,11 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
       {d->materials, sizeof(rtc_material) * d->n_materials, 0},
       {d->patterns, sizeof(rtc_pattern) * d->n_patterns, 0},
       {d->lights, sizeof(rtc_light) * d->n_lights, 0},
-      {csg_parent.data(), sizeof(int32_t) * csg_parent.size(), 0}};
+      {csg_parent.data(), sizeof(int32_t) * csg_parent.size(), 0},
+      {accel.parent.data(), sizeof(int32_t) * accel.parent.size(), 0},
+      {accel.always.data(), sizeof(int32_t) * accel.always.size(), 0},
+      {accel.bvh_prims.data(), sizeof(int32_t) * accel.bvh_prims.size(), 0},
+      {accel.bvh.data(), sizeof(BvhNode) * accel.bvh.size(), 0}};
   size_t total = 0;
   for (auto& p : parts) {
     if (p.bytes && !p.src) return fail(RTC_ERR_INVALID, "a non-empty table has a NULL pointer");
@@ -261,6 +264,12 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   v.patterns = (const rtc_pattern*)(s->slab + parts[7].off);
   v.lights = (const rtc_light*)(s->slab + parts[8].off);
   v.csg_parent = (const int32_t*)(s->slab + parts[9].off);
+  v.parent = (const int32_t*)(s->slab + parts[10].off);
+  v.always = (const int32_t*)(s->slab + parts[11].off);
+  v.bvh_prims = (const int32_t*)(s->slab + parts[12].off);
+  v.bvh = (const BvhNode*)(s->slab + parts[13].off);
+  v.n_always = (int32_t)accel.always.size();
+  v.n_bvh = (int32_t)accel.bvh.size();
   v.n_nodes = (int32_t)d->n_nodes;
   v.n_lights = (int32_t)d->n_lights;
   v.has_csg = has_csg ? 1 : 0;
@@ -392,8 +401,8 @@ int rtc_trace_rays(rtc_scene* s, size_t n, const double* origins, const double* 
   TRY_OR_CLEAN(cudaMemcpyAsync(d_d, directions, 3 * n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
   TRY_OR_CLEAN(cudaMemsetAsync(s->d_counters, 0, N_COUNTERS * sizeof(unsigned long long), s->stream));
   unsigned blocks = (unsigned)((n + 127) / 128);
-  if (s->has_csg) trace_kernel<true, true><<<blocks, 128, 0, s->stream>>>(s->view, n, d_o, d_d, (int)remaining, d_rgb, d_t, s->d_counters);
-  else trace_kernel<false, true><<<blocks, 128, 0, s->stream>>>(s->view, n, d_o, d_d, (int)remaining, d_rgb, d_t, s->d_counters);
+  if (s->has_csg) trace_kernel<true><<<blocks, 128, 0, s->stream>>>(s->view, n, d_o, d_d, (int)remaining, d_rgb, d_t, s->d_counters);
+  else trace_kernel<false><<<blocks, 128, 0, s->stream>>>(s->view, n, d_o, d_d, (int)remaining, d_rgb, d_t, s->d_counters);
   TRY_OR_CLEAN(cudaGetLastError());
   if (rgb_out) TRY_OR_CLEAN(cudaMemcpyAsync(rgb_out, d_rgb, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
   if (t_out) TRY_OR_CLEAN(cudaMemcpyAsync(t_out, d_t, n * sizeof(double), cudaMemcpyDeviceToHost, s->stream));

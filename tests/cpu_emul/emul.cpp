@@ -16,6 +16,7 @@ namespace {
 struct Built {
   SceneView view;
   std::vector<int32_t> csg_parent;
+  AccelBuild accel;
 };
 void build_view(const rtc_scene_desc* d, Built& b) {
   const int32_t n = (int32_t)d->n_nodes;
@@ -36,6 +37,9 @@ void build_view(const rtc_scene_desc* d, Built& b) {
   v.tri_geom = d->tri_p1e1e2; v.tri_normals = d->tri_normals; v.materials = d->materials;
   v.patterns = d->patterns; v.lights = d->lights; v.csg_parent = b.csg_parent.data();
   v.n_nodes = n; v.n_lights = (int32_t)d->n_lights; v.has_csg = has_csg ? 1 : 0; v._pad = 0;
+  build_accel(d, b.accel);
+  v.parent = b.accel.parent.data(); v.always = b.accel.always.data(); v.bvh_prims = b.accel.bvh_prims.data();
+  v.bvh = b.accel.bvh.data(); v.n_always = (int32_t)b.accel.always.size(); v.n_bvh = (int32_t)b.accel.bvh.size();
 }
 CameraD make_cam(const rtc_camera* c) {
   CameraD cam;
@@ -48,8 +52,8 @@ CameraD make_cam(const rtc_camera* c) {
   cam.hsize = c->hsize; cam.vsize = c->vsize;
   return cam;
 }
-template <bool CSG, bool FA>
-void rows(const SceneView& S, const CameraD& cam, uint32_t y0, uint32_t y1, uint32_t aa, bool avg, int depth, double* out,
+template <bool CSG>
+void rows(const SceneView& S, const CameraD& cam, uint32_t y0, uint32_t y1, uint32_t aa, bool avg, int depth, bool fa, double* out,
           uint64_t* counters) {
   Scratch<CSG>* scratch = new Scratch<CSG>();
   RayCounters rc = {0, 0, 0, 0};
@@ -57,7 +61,7 @@ void rows(const SceneView& S, const CameraD& cam, uint32_t y0, uint32_t y1, uint
   for (uint32_t y = y0; y < y1; y++)
     for (uint32_t x = 0; x < cam.hsize; x++) {
       uint32_t err = 0;
-      V3 c = render_pixel<CSG, FA>(S, cam, x, y, aa, avg, depth, *scratch, rc, &err);
+      V3 c = render_pixel<CSG>(S, cam, x, y, aa, avg, depth, fa, *scratch, rc, &err);
       double* o = out + ((size_t)y * cam.hsize + x) * 3;
       o[0] = c.x; o[1] = c.y; o[2] = c.z;
       if (err & ERR_OVERFLOW) ovf++;
@@ -91,10 +95,8 @@ int emul_render(const rtc_scene_desc* d, const rtc_camera* c, const rtc_opts* o,
     th.emplace_back([&, t]() {
       // interleaved rows for load balance
       for (uint32_t y = y0 + t; y < y1; y += threads) {
-        if (b.view.has_csg) { if (fa) rows<true, true>(b.view, cam, y, y + 1, o->aa_samples, avg, (int)o->max_depth, rgb, per[t].data());
-                              else rows<true, false>(b.view, cam, y, y + 1, o->aa_samples, avg, (int)o->max_depth, rgb, per[t].data()); }
-        else { if (fa) rows<false, true>(b.view, cam, y, y + 1, o->aa_samples, avg, (int)o->max_depth, rgb, per[t].data());
-               else rows<false, false>(b.view, cam, y, y + 1, o->aa_samples, avg, (int)o->max_depth, rgb, per[t].data()); }
+        if (b.view.has_csg) rows<true>(b.view, cam, y, y + 1, o->aa_samples, avg, (int)o->max_depth, fa, rgb, per[t].data());
+        else rows<false>(b.view, cam, y, y + 1, o->aa_samples, avg, (int)o->max_depth, fa, rgb, per[t].data());
       }
     });
   }
@@ -115,8 +117,8 @@ int emul_trace_rays(const rtc_scene_desc* d, size_t n, const double* origins, co
     r.d = v3(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]);
     double t = -1.0;
     V3 c;
-    if (b.view.has_csg) { Scratch<true> s; c = color_at<true, true>(b.view, r, (int)remaining, s, rc, &err, &t); }
-    else { Scratch<false> s; c = color_at<false, true>(b.view, r, (int)remaining, s, rc, &err, &t); }
+    if (b.view.has_csg) { Scratch<true> s; c = color_at<true>(b.view, r, (int)remaining, true, s, rc, &err, &t); }
+    else { Scratch<false> s; c = color_at<false>(b.view, r, (int)remaining, true, s, rc, &err, &t); }
     if (rgb) { rgb[3 * i] = c.x; rgb[3 * i + 1] = c.y; rgb[3 * i + 2] = c.z; }
     if (t_out) t_out[i] = t;
   }
@@ -133,17 +135,17 @@ int emul_probe_hit(const rtc_scene_desc* d, const double* o, const double* dir, 
   for (int i = 0; i < 20; i++) out[i] = 0.0;
   uint32_t err = 0;
   Scratch<true> scratch;
-  ClosestHit ch;
-  ch.init();
-  walk_scene<true, true>(S, ray, ch, scratch.csg(), &err);
-  if (ch.best_node < 0) return (int)err;
-  rtc_node nd = load_node(S.nodes + ch.best_node);
+  Query ch;
+  ch.init_closest(&err);
+  search<true>(S, ray, ch, scratch.csg(), &scratch.bvh, true, &err);
+  if (ch.node < 0) return (int)err;
+  rtc_node nd = load_node(S.nodes + ch.node);
   Comps c;
-  prepare(S, ray, ch.best_t, ch.best_node, nd, c);
-  NegCollect nc;
-  nc.init(&scratch.neg, &err);
-  walk_scene<true, true>(S, ray, nc, scratch.csg(), &err);
-  containers_n1n2(S, scratch.neg, ch.best_node, c.n1, c.n2, &err);
+  prepare(S, ray, ch.limit, ch.node, nd, c);
+  Query nc;
+  nc.init_neg(&scratch.neg, &err);
+  search<true>(S, ray, nc, scratch.csg(), &scratch.bvh, true, &err);
+  containers_n1n2(S, scratch.neg, ch.node, c.n1, c.n2, &err);
   out[0] = 1.0; out[1] = c.t;
   out[2] = c.point.x; out[3] = c.point.y; out[4] = c.point.z;
   out[5] = c.normalv.x; out[6] = c.normalv.y; out[7] = c.normalv.z;
@@ -160,8 +162,15 @@ int emul_is_shadowed(const rtc_scene_desc* d, const double* p, uint32_t light) {
   uint32_t err = 0;
   Scratch<true> scratch;
   const rtc_light& L = d->lights[light];
-  return is_shadowed<true, true>(b.view, v3(p[0], p[1], p[2]), v3(L.position[0], L.position[1], L.position[2]),
-                                 scratch.csg(), &err) ? 1 : 0;
+  V3 lp = v3(L.position[0], L.position[1], L.position[2]), pt = v3(p[0], p[1], p[2]);
+  V3 v = lp - pt;
+  RayD r;
+  r.o = pt;
+  r.d = normalize(v);
+  Query sh;
+  sh.init_shadow(magnitude(v), &err);
+  search<true>(b.view, r, sh, scratch.csg(), &scratch.bvh, true, &err);
+  return sh.done() ? 1 : 0;
 }
 
 }  // extern "C"
