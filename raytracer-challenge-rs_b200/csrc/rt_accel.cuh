@@ -28,17 +28,24 @@ struct BvhStack {
 
 // Has `ray` passed the box of every reference Group enclosing `node`? `ok_group`: innermost group
 // already validated for this ray (its ancestors are then valid too), -1 initially (= top level).
-RTC_HD bool chain_ok(const SceneView& S, int32_t node, const RayD& ray, int32_t& ok_group) {
-  int32_t g0 = RTC_LDG(S.parent + node);
-  int32_t g = g0;
-  RTK_COUNT(chain_calls, 1);
+// The slow part is rare (only for candidates the query wants) and kept out of line: it is six
+// IEEE divisions per box, and inlining it at every candidate site bloats the hot loop.
+RTC_HD_NOINLINE bool chain_walk(const int32_t* parent, const rtc_node* nodes, const double* boxes, int32_t g, int32_t ok_group,
+                                RayD ray) {
   while (g >= 0 && g != ok_group) {
     double tmin, tmax;
     RTK_COUNT(chain_boxes, 1);
-    int32_t bx = RTC_LDG(&S.nodes[g].aux);
-    if (!box_intersects(S.boxes + 6 * (size_t)bx, ray, tmin, tmax)) return false;
-    g = RTC_LDG(S.parent + g);
+    int32_t bx = RTC_LDG(&nodes[g].aux);
+    if (!box_intersects(boxes + 6 * (size_t)bx, ray, tmin, tmax)) return false;
+    g = RTC_LDG(parent + g);
   }
+  return true;
+}
+RTC_HD bool chain_ok(const SceneView& S, int32_t node, const RayD& ray, int32_t& ok_group) {
+  const int32_t g0 = RTC_LDG(S.parent + node);
+  RTK_COUNT(chain_calls, 1);
+  if (g0 == ok_group) return true;
+  if (!chain_walk(S.parent, S.nodes, S.boxes, g0, ok_group, ray)) return false;
   ok_group = g0;
   return true;
 }
@@ -55,115 +62,114 @@ RTC_HD bool own_box(const double* lo, const double* hi, const RayD& r, V3 inv, d
   return tmin <= tmax + 1e-9 * (fabs(tmin) + fabs(tmax));
 }
 
-// One candidate intersection of leaf `i` (chain node `i`): NaN bookkeeping, want → validate → take.
-RTC_HD void offer(const SceneView& S, const RayD& ray, Query& C, double t, int32_t i, uint32_t flags, int32_t& ok_group,
-                  uint32_t* err) {
-  if (t != t) { if (chain_ok(S, i, ray, ok_group)) *err |= ERR_NAN; return; }
-  if (!C.want(t, i, flags)) return;
-  if (!chain_ok(S, i, ray, ok_group)) return;
-  C.take(t, i);
-}
-
-RTC_HD void test_leaf(const SceneView& S, const RayD& ray, Query& C, int32_t i, const rtc_node& nd, RayD& lr, int32_t& lr_xf,
-                      int32_t& ok_group, uint32_t* err) {
-  if (nd.xform != lr_xf) {
-    lr = ray_transform(S.xforms + 12 * (size_t)nd.xform, ray);
-    lr_xf = nd.xform;
-  }
-  LeafHits h;
-  isect_leaf(S, nd, lr, h);
-  if (h.n > 0) offer(S, ray, C, h.t0, i, nd.flags, ok_group, err);
-  if (h.n > 1) offer(S, ray, C, h.t1, i, nd.flags, ok_group, err);
-  if (h.n > 2) offer(S, ray, C, h.t2, i, nd.flags, ok_group, err);
-  if (h.n > 3) offer(S, ray, C, h.t3, i, nd.flags, ok_group, err);
-}
-
-// World::intersect → query. faithful: the reference's own search order, node by node.
-template <bool HAS_CSG>
-RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs, BvhStack* st, bool faithful, uint32_t* err) {
-  int32_t ok_group = -1;
-  RayD lr;
-  int32_t lr_xf = -1;
+// World::intersect → query. FAITHFUL: the reference's own search order, node by node (walk_range
+// over the whole array). Otherwise: the prims tested for every ray, then the BVH; ONE leaf-test
+// site and ONE candidate site serve both, so the hot loop stays small.
+template <bool HAS_CSG, bool FAITHFUL>
+RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs, BvhStack* st, uint32_t* err) {
   RTK_COUNT(walks, 1);
-
-  // ---- prims tested for every ray (faithful: one "prim" = the whole node array) ------------------
-  const int32_t n_always = faithful ? 1 : S.n_always;
-  for (int32_t k = 0; k < n_always && !C.done(); k++) {
-    int32_t i = 0, end = S.n_nodes;
-    bool range = true;
-    rtc_node nd;
-    if (!faithful) {
-      i = RTC_LDG(S.always + k);
-      nd = load_node(S.nodes + i);
-      RTK_COUNT(always_tests, 1);
-      range = nd.kind == RTC_CSG;
-      end = nd.skip;
-      // the reference reaches this CSG only through its enclosing groups: validate first
-      if (range && !chain_ok(S, i, ray, ok_group)) continue;
-    }
-    if (range) {
-      walk_range<HAS_CSG>(S, ray, C, cs, err, i, end);
-      continue;
-    }
-    test_leaf(S, ray, C, i, nd, lr, lr_xf, ok_group, err);
-  }
-  if (faithful || S.n_bvh <= 0 || C.done()) return;
-
-  // ---- BVH over triangles and spheres: refs >= 0 inner node, < 0 leaf ~(first << 3 | count) --------
-  const V3 inv = v3(1.0 / ray.d.x, 1.0 / ray.d.y, 1.0 / ray.d.z);
-  int sp = 0;
-  int32_t cur = 0;
-  for (;;) {
-    if (cur < 0) {
-      const int32_t ref = ~cur, first = ref >> 3, count = ref & 7;
-      for (int32_t k = first; k < first + count; k++) {
-        const int32_t i = RTC_LDG(S.bvh_prims + k);
-        rtc_node nd = load_node(S.nodes + i);
-        RTK_COUNT(prim_tests, 1);
-        test_leaf(S, ray, C, i, nd, lr, lr_xf, ok_group, err);
-      }
-      if (C.done()) return;
-      cur = 0;
-      bool got = false;
-      while (sp > 0) {
-        sp--;
-        if (!C.cull(st->tmin[sp], rt_inf())) { cur = st->node[sp]; got = true; break; }
-      }
-      if (!got) return;
-      continue;
-    }
-    const BvhNode* bn = S.bvh + cur;
-    RTK_COUNT(bvh_nodes, 1);
-#if defined(__CUDA_ARCH__)
-    const int4 ci = __ldg(reinterpret_cast<const int4*>(&bn->c0));
-    const int32_t c0 = ci.x, n0 = ci.y, c1 = ci.z, n1 = ci.w;
-#else
-    const int32_t c0 = bn->c0, n0 = bn->n0, c1 = bn->c1, n1 = bn->n1;
+  if constexpr (FAITHFUL) {
+    (void)st;
+    walk_range<HAS_CSG>(S, ray, C, cs, err, 0, S.n_nodes);
+    return;
+  } else {
+    int32_t ok_group = -1;
+    RayD lr;
+    int32_t lr_xf = -1;
+    V3 inv = v3(0.0, 0.0, 0.0);
+    bool have_inv = false;
+    int sp = 0;
+    // current item: a run of prims [first, first+count) (leaf) or a BVH node (cur >= 0)
+    int32_t first = 0, count = S.n_always, cur = -1;
+    for (;;) {
+      if (cur < 0) {
+        for (int32_t k = first; k < first + count && !C.done(); k++) {
+          const int32_t i = RTC_LDG(S.prims + k);
+          const rtc_node nd = load_node(S.nodes + i);
+          RTK_COUNT(prim_tests, 1);
+          if (nd.kind == RTC_CSG) {
+            if constexpr (HAS_CSG) {
+              // the reference reaches this CSG only through its enclosing groups: validate first
+              if (chain_ok(S, i, ray, ok_group)) walk_range<true>(S, ray, C, cs, err, i, nd.skip);
+            }
+            continue;
+          }
+          if (nd.xform != lr_xf) {
+            lr = ray_transform(S.xforms + 12 * (size_t)nd.xform, ray);
+            lr_xf = nd.xform;
+          }
+          LeafHits h;
+          isect_leaf(S, nd, lr, h);
+#if defined(__CUDACC__)
+#pragma unroll 1
 #endif
-    double t0min = 0.0, t0max = 0.0, t1min = 0.0, t1max = 0.0;
-    const bool h0 = n0 >= 0 && own_box(bn->lo0, bn->hi0, ray, inv, t0min, t0max) && !C.cull(t0min, t0max);
-    const bool h1 = n1 >= 0 && own_box(bn->lo1, bn->hi1, ray, inv, t1min, t1max) && !C.cull(t1min, t1max);
-    const int32_t r0 = n0 > 0 ? ~((c0 << 3) | n0) : c0;
-    const int32_t r1 = n1 > 0 ? ~((c1 << 3) | n1) : c1;
-    if (h0 && h1) {
-      const bool swap = t1min < t0min;   // near child first, far child on the stack with its tmin
-      if (sp < BVH_STACK) {
-        st->node[sp] = swap ? r0 : r1;
-        st->tmin[sp] = swap ? t0min : t1min;
-        sp++;
+          for (int j = 0; j < h.n; j++) {
+            const double t = j == 0 ? h.t0 : (j == 1 ? h.t1 : (j == 2 ? h.t2 : h.t3));
+            if (t != t) { if (chain_ok(S, i, ray, ok_group)) *err |= ERR_NAN; continue; }
+            if (!C.want(t, i, nd.flags)) continue;
+            if (!chain_ok(S, i, ray, ok_group)) continue;
+            C.take(t, i);
+          }
+        }
+        if (C.done() || S.n_bvh <= 0) return;
+        if (!have_inv) {  // the always-run is done: enter the BVH at its root
+          inv = v3(1.0 / ray.d.x, 1.0 / ray.d.y, 1.0 / ray.d.z);
+          have_inv = true;
+          cur = 0;
+          continue;
+        }
       } else {
-        *err |= ERR_OVERFLOW;
+        const BvhNode* bn = S.bvh + cur;
+        RTK_COUNT(bvh_nodes, 1);
+#if defined(__CUDA_ARCH__)
+        const int4 ci = __ldg(reinterpret_cast<const int4*>(&bn->c0));
+        const int32_t c0 = ci.x, n0 = ci.y, c1 = ci.z, n1 = ci.w;
+#else
+        const int32_t c0 = bn->c0, n0 = bn->n0, c1 = bn->c1, n1 = bn->n1;
+#endif
+        double t0min = 0.0, t0max = 0.0, t1min = 0.0, t1max = 0.0;
+        const bool h0 = n0 >= 0 && own_box(bn->lo0, bn->hi0, ray, inv, t0min, t0max) && !C.cull(t0min, t0max);
+        const bool h1 = n1 >= 0 && own_box(bn->lo1, bn->hi1, ray, inv, t1min, t1max) && !C.cull(t1min, t1max);
+        // refs: >= 0 inner node, < 0 leaf ~(first << 3 | count)
+        const int32_t r0 = n0 > 0 ? ~((c0 << 3) | n0) : c0;
+        const int32_t r1 = n1 > 0 ? ~((c1 << 3) | n1) : c1;
+        cur = -1;
+        count = 0;
+        if (h0 && h1) {
+          const bool swap = t1min < t0min;  // near child first, far child on the stack with its tmin
+          if (sp < BVH_STACK) {
+            st->node[sp] = swap ? r0 : r1;
+            st->tmin[sp] = swap ? t0min : t1min;
+            sp++;
+          } else {
+            *err |= ERR_OVERFLOW;
+          }
+          cur = swap ? r1 : r0;
+        } else if (h0 || h1) {
+          cur = h0 ? r0 : r1;
+        }
+        if (cur >= 0) continue;           // descend into an inner node
+        if (h0 || h1) {                   // a leaf: decode and test it next iteration
+          const int32_t ref = ~cur;
+          first = ref >> 3;
+          count = ref & 7;
+          cur = -1;
+          continue;
+        }
       }
-      cur = swap ? r1 : r0;
-    } else if (h0 || h1) {
-      cur = h0 ? r0 : r1;
-    } else {
+      // pop
       bool got = false;
       while (sp > 0) {
         sp--;
         if (!C.cull(st->tmin[sp], rt_inf())) { cur = st->node[sp]; got = true; break; }
       }
       if (!got) return;
+      if (cur < 0) {
+        const int32_t ref = ~cur;
+        first = ref >> 3;
+        count = ref & 7;
+        cur = -1;
+      }
     }
   }
 }

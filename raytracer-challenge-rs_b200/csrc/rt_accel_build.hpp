@@ -39,8 +39,8 @@ struct BvhNode {     // 128 bytes: both children's boxes in one fetch
 
 struct AccelBuild {
   std::vector<int32_t> parent;     // per node: innermost enclosing Group node (outside CSGs), or -1
-  std::vector<int32_t> always;     // node indices, ascending
-  std::vector<int32_t> bvh_prims;  // node indices in BVH leaf order
+  std::vector<int32_t> prims;      // node indices: [0, n_always) tested for every ray (ascending), then BVH leaf order
+  int32_t n_always = 0;
   std::vector<BvhNode> bvh;        // node 0 = root (empty vector: no BVH)
   int32_t max_depth = 0;
 };
@@ -258,8 +258,13 @@ struct Builder {
         stack.push_back({mid, t.e, id, 1, t.depth + 1});
       }
     }
-    out.bvh_prims.resize((size_t)n);
-    for (int k = 0; k < n; k++) out.bvh_prims[(size_t)k] = prims[(size_t)k].node;
+    // BVH leaves address the combined prim array: shift by the always-prefix
+    const int32_t shift = (int32_t)out.prims.size();
+    for (auto& nd : out.bvh) {
+      if (nd.n0 > 0) nd.c0 += shift;
+      if (nd.n1 > 0) nd.c1 += shift;
+    }
+    for (int k = 0; k < n; k++) out.prims.push_back(prims[(size_t)k].node);
   }
 };
 
@@ -272,8 +277,8 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
   using namespace accel_detail;
   const int32_t n = (int32_t)d->n_nodes;
   A.parent.assign((size_t)n, -1);
-  A.always.clear();
-  A.bvh_prims.clear();
+  A.prims.clear();
+  A.n_always = 0;
   A.bvh.clear();
   std::vector<Prim> cand;
   struct Open { int32_t end, node; };
@@ -287,7 +292,7 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
       if (nd.skip > i + 1) groups.push_back({nd.skip, i});
       i = i + 1;
     } else if (nd.kind == RTC_CSG) {
-      A.always.push_back(i);
+      A.prims.push_back(i);
       i = nd.skip;  // the subtree is evaluated by the in-order walk
     } else {
       Prim p;
@@ -296,16 +301,18 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
         for (int a = 0; a < 3; a++) p.c[a] = 0.5 * (p.box.lo[a] + p.box.hi[a]);
         cand.push_back(p);
       } else {
-        A.always.push_back(i);
+        A.prims.push_back(i);
       }
       i = i + 1;
     }
   }
   if ((int)cand.size() < BVH_MIN_PRIMS) {
-    for (auto& p : cand) A.always.push_back(p.node);
-    std::sort(A.always.begin(), A.always.end());
+    for (auto& p : cand) A.prims.push_back(p.node);
+    std::sort(A.prims.begin(), A.prims.end());
+    A.n_always = (int32_t)A.prims.size();
     return;
   }
+  A.n_always = (int32_t)A.prims.size();
   Builder b(cand, A);
   b.build();
 }

@@ -26,8 +26,7 @@ struct SceneView {
   const int32_t* csg_parent; // per node: nearest enclosing CSG node, or -1
   // traversal accelerator (rt_accel_build.hpp)
   const int32_t* parent;     // per node: innermost enclosing reference Group (outside CSGs), or -1
-  const int32_t* always;     // prims tested for every ray (node indices, ascending)
-  const int32_t* bvh_prims;  // node indices in BVH leaf order
+  const int32_t* prims;      // node indices: [0, n_always) tested for every ray, then BVH leaf order
   const BvhNode* bvh;        // binary BVH, node 0 = root
   int32_t n_nodes;
   int32_t n_lights;

@@ -257,7 +257,6 @@ enum : int { PH_CLOSEST = 0, PH_SHADOW = 1, PH_NEG = 2 };
 enum : int { NX_RETURN = 0, NX_SHADOW = 1, NX_LIT = 2, NX_N1N2 = 3 };
 
 struct Tracer {
-  Frame frames[MAX_FRAMES];
   RayD ray;        // the ray color_at is being evaluated for (current recursion level)
   RayD qray;       // the ray of the pending query
   Query q;
@@ -284,7 +283,7 @@ struct Tracer {
 
   // Consume the answer of the pending query; set up the next one. Returns true when color_at of the
   // primary ray is complete (`result`).
-  RTC_HD bool advance(const SceneView& S, HitList& neg, RayCounters& rc, uint32_t* err) {
+  RTC_HD bool advance(const SceneView& S, Frame* frames, HitList& neg, RayCounters& rc, uint32_t* err) {
     int next;
     if (phase == PH_CLOSEST) {
       if (sp == 0) t_primary = q.node >= 0 ? q.limit : -1.0;
@@ -405,14 +404,15 @@ struct Tracer {
   }
 };
 
-template <bool HAS_CSG>
-RTC_HD V3 color_at(const SceneView& S, const RayD& ray, int max_depth, bool faithful, Scratch<HAS_CSG>& scratch, RayCounters& rc,
+template <bool HAS_CSG, bool FAITHFUL>
+RTC_HD V3 color_at(const SceneView& S, const RayD& ray, int max_depth, Scratch<HAS_CSG>& scratch, RayCounters& rc,
                    uint32_t* err, double* t_out = nullptr) {
   Tracer tr;
+  Frame frames[MAX_FRAMES];  // kept out of Tracer: a dynamically indexed member would pin the whole struct in local memory
   tr.start(ray, max_depth, err);
   for (;;) {
-    search<HAS_CSG>(S, tr.qray, tr.q, scratch.csg(), &scratch.bvh, faithful, err);
-    if (tr.advance(S, scratch.neg, rc, err)) break;
+    search<HAS_CSG, FAITHFUL>(S, tr.qray, tr.q, scratch.csg(), &scratch.bvh, err);
+    if (tr.advance(S, frames, scratch.neg, rc, err)) break;
   }
   if (t_out) *t_out = tr.t_primary;
   return tr.result;
@@ -459,19 +459,19 @@ RTC_HD void aa_offset(uint32_t aa, uint32_t s, double& ox, double& oy) {
 
 // One pixel of Camera::render (aa==1, camera.rs:133-148: colour stored as is) or of
 // render_multithreaded (camera.rs:178-187: Color::average = sequential sum * (1.0/n)).
-template <bool HAS_CSG>
+template <bool HAS_CSG, bool FAITHFUL>
 RTC_HD V3 render_pixel(const SceneView& S, const CameraD& cam, uint32_t px, uint32_t py, uint32_t aa, bool average,
-                       int max_depth, bool faithful, Scratch<HAS_CSG>& scratch, RayCounters& rc, uint32_t* err) {
+                       int max_depth, Scratch<HAS_CSG>& scratch, RayCounters& rc, uint32_t* err) {
   if (!average) {
     rc.primary++;
-    return color_at<HAS_CSG>(S, ray_for_pixel(cam, px, py, 0.5, 0.5), max_depth, faithful, scratch, rc, err);
+    return color_at<HAS_CSG, FAITHFUL>(S, ray_for_pixel(cam, px, py, 0.5, 0.5), max_depth, scratch, rc, err);
   }
   V3 avg = v3(0.0, 0.0, 0.0);
   for (uint32_t s = 0; s < aa; s++) {
     double ox, oy;
     aa_offset(aa, s, ox, oy);
     rc.primary++;
-    avg = avg + color_at<HAS_CSG>(S, ray_for_pixel(cam, px, py, ox, oy), max_depth, faithful, scratch, rc, err);
+    avg = avg + color_at<HAS_CSG, FAITHFUL>(S, ray_for_pixel(cam, px, py, ox, oy), max_depth, scratch, rc, err);
   }
   return avg * (1.0 / (double)aa);
 }

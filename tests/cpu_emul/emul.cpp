@@ -38,8 +38,8 @@ void build_view(const rtc_scene_desc* d, Built& b) {
   v.patterns = d->patterns; v.lights = d->lights; v.csg_parent = b.csg_parent.data();
   v.n_nodes = n; v.n_lights = (int32_t)d->n_lights; v.has_csg = has_csg ? 1 : 0; v._pad = 0;
   build_accel(d, b.accel);
-  v.parent = b.accel.parent.data(); v.always = b.accel.always.data(); v.bvh_prims = b.accel.bvh_prims.data();
-  v.bvh = b.accel.bvh.data(); v.n_always = (int32_t)b.accel.always.size(); v.n_bvh = (int32_t)b.accel.bvh.size();
+  v.parent = b.accel.parent.data(); v.prims = b.accel.prims.data();
+  v.bvh = b.accel.bvh.data(); v.n_always = b.accel.n_always; v.n_bvh = (int32_t)b.accel.bvh.size();
 }
 CameraD make_cam(const rtc_camera* c) {
   CameraD cam;
@@ -52,8 +52,8 @@ CameraD make_cam(const rtc_camera* c) {
   cam.hsize = c->hsize; cam.vsize = c->vsize;
   return cam;
 }
-template <bool CSG>
-void rows(const SceneView& S, const CameraD& cam, uint32_t y0, uint32_t y1, uint32_t aa, bool avg, int depth, bool fa, double* out,
+template <bool CSG, bool FA>
+void rows(const SceneView& S, const CameraD& cam, uint32_t y0, uint32_t y1, uint32_t aa, bool avg, int depth, double* out,
           uint64_t* counters) {
   Scratch<CSG>* scratch = new Scratch<CSG>();
   RayCounters rc = {0, 0, 0, 0};
@@ -61,7 +61,7 @@ void rows(const SceneView& S, const CameraD& cam, uint32_t y0, uint32_t y1, uint
   for (uint32_t y = y0; y < y1; y++)
     for (uint32_t x = 0; x < cam.hsize; x++) {
       uint32_t err = 0;
-      V3 c = render_pixel<CSG>(S, cam, x, y, aa, avg, depth, fa, *scratch, rc, &err);
+      V3 c = render_pixel<CSG, FA>(S, cam, x, y, aa, avg, depth, *scratch, rc, &err);
       double* o = out + ((size_t)y * cam.hsize + x) * 3;
       o[0] = c.x; o[1] = c.y; o[2] = c.z;
       if (err & ERR_OVERFLOW) ovf++;
@@ -95,8 +95,10 @@ int emul_render(const rtc_scene_desc* d, const rtc_camera* c, const rtc_opts* o,
     th.emplace_back([&, t]() {
       // interleaved rows for load balance
       for (uint32_t y = y0 + t; y < y1; y += threads) {
-        if (b.view.has_csg) rows<true>(b.view, cam, y, y + 1, o->aa_samples, avg, (int)o->max_depth, fa, rgb, per[t].data());
-        else rows<false>(b.view, cam, y, y + 1, o->aa_samples, avg, (int)o->max_depth, fa, rgb, per[t].data());
+        if (b.view.has_csg) { if (fa) rows<true, true>(b.view, cam, y, y + 1, o->aa_samples, avg, (int)o->max_depth, rgb, per[t].data());
+                              else rows<true, false>(b.view, cam, y, y + 1, o->aa_samples, avg, (int)o->max_depth, rgb, per[t].data()); }
+        else { if (fa) rows<false, true>(b.view, cam, y, y + 1, o->aa_samples, avg, (int)o->max_depth, rgb, per[t].data());
+               else rows<false, false>(b.view, cam, y, y + 1, o->aa_samples, avg, (int)o->max_depth, rgb, per[t].data()); }
       }
     });
   }
@@ -117,8 +119,8 @@ int emul_trace_rays(const rtc_scene_desc* d, size_t n, const double* origins, co
     r.d = v3(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]);
     double t = -1.0;
     V3 c;
-    if (b.view.has_csg) { Scratch<true> s; c = color_at<true>(b.view, r, (int)remaining, true, s, rc, &err, &t); }
-    else { Scratch<false> s; c = color_at<false>(b.view, r, (int)remaining, true, s, rc, &err, &t); }
+    if (b.view.has_csg) { Scratch<true> s; c = color_at<true, true>(b.view, r, (int)remaining, s, rc, &err, &t); }
+    else { Scratch<false> s; c = color_at<false, true>(b.view, r, (int)remaining, s, rc, &err, &t); }
     if (rgb) { rgb[3 * i] = c.x; rgb[3 * i + 1] = c.y; rgb[3 * i + 2] = c.z; }
     if (t_out) t_out[i] = t;
   }
@@ -137,14 +139,14 @@ int emul_probe_hit(const rtc_scene_desc* d, const double* o, const double* dir, 
   Scratch<true> scratch;
   Query ch;
   ch.init_closest(&err);
-  search<true>(S, ray, ch, scratch.csg(), &scratch.bvh, true, &err);
+  search<true, true>(S, ray, ch, scratch.csg(), &scratch.bvh, &err);
   if (ch.node < 0) return (int)err;
   rtc_node nd = load_node(S.nodes + ch.node);
   Comps c;
   prepare(S, ray, ch.limit, ch.node, nd, c);
   Query nc;
   nc.init_neg(&scratch.neg, &err);
-  search<true>(S, ray, nc, scratch.csg(), &scratch.bvh, true, &err);
+  search<true, true>(S, ray, nc, scratch.csg(), &scratch.bvh, &err);
   containers_n1n2(S, scratch.neg, ch.node, c.n1, c.n2, &err);
   out[0] = 1.0; out[1] = c.t;
   out[2] = c.point.x; out[3] = c.point.y; out[4] = c.point.z;
@@ -169,7 +171,7 @@ int emul_is_shadowed(const rtc_scene_desc* d, const double* p, uint32_t light) {
   r.d = normalize(v);
   Query sh;
   sh.init_shadow(magnitude(v), &err);
-  search<true>(b.view, r, sh, scratch.csg(), &scratch.bvh, true, &err);
+  search<true, true>(b.view, r, sh, scratch.csg(), &scratch.bvh, &err);
   return sh.done() ? 1 : 0;
 }
 
