@@ -41,8 +41,7 @@ RTC_HD_NOINLINE bool chain_walk(const int32_t* parent, const rtc_node* nodes, co
   }
   return true;
 }
-RTC_HD bool chain_ok(const SceneView& S, int32_t node, const RayD& ray, int32_t& ok_group) {
-  const int32_t g0 = RTC_LDG(S.parent + node);
+RTC_HD bool chain_ok(const SceneView& S, int32_t g0, const RayD& ray, int32_t& ok_group) {
   RTK_COUNT(chain_calls, 1);
   if (g0 == ok_group) return true;
   if (!chain_walk(S.parent, S.nodes, S.boxes, g0, ok_group, ray)) return false;
@@ -84,19 +83,35 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
     for (;;) {
       if (cur < 0) {
         for (int32_t k = first; k < first + count && !C.done(); k++) {
-          const int32_t i = RTC_LDG(S.prims + k);
-          const rtc_node nd = load_node(S.nodes + i);
+          int32_t i, par;
+          rtc_node nd;
           RTK_COUNT(prim_tests, 1);
-          if (nd.kind == RTC_CSG) {
-            if constexpr (HAS_CSG) {
-              // the reference reaches this CSG only through its enclosing groups: validate first
-              if (chain_ok(S, i, ray, ok_group)) walk_range<true>(S, ray, C, cs, err, i, nd.skip);
+          if (k < S.n_always) {  // (uniform per run) every-ray prim: one 128-byte record
+            const PrimRec* rec = S.recs + k;
+#if defined(__CUDA_ARCH__)
+            const int4 hd = __ldg(reinterpret_cast<const int4*>(rec));
+            i = hd.x; nd.kind = hd.y; nd.aux = hd.z; par = hd.w;
+#else
+            i = rec->node; nd.kind = rec->kind; nd.aux = rec->aux; par = rec->parent;
+#endif
+            nd.flags = RTC_LDG(&rec->flags);
+            if (nd.kind == RTC_CSG) {
+              if constexpr (HAS_CSG) {
+                // the reference reaches this CSG only through its enclosing groups: validate first
+                if (chain_ok(S, par, ray, ok_group)) walk_range<true>(S, ray, C, cs, err, i, RTC_LDG(&S.nodes[i].skip));
+              }
+              continue;
             }
-            continue;
-          }
-          if (nd.xform != lr_xf) {
-            lr = ray_transform(S.xforms + 12 * (size_t)nd.xform, ray);
-            lr_xf = nd.xform;
+            lr = ray_transform_v2(rec->inv, ray);
+            lr_xf = -1;
+          } else {
+            i = RTC_LDG(S.prims + k);
+            nd = load_node(S.nodes + i);
+            par = -2;  // loaded on demand
+            if (nd.xform != lr_xf) {
+              lr = ray_transform(S.xforms + 12 * (size_t)nd.xform, ray);
+              lr_xf = nd.xform;
+            }
           }
           LeafHits h;
           isect_leaf(S, nd, lr, h);
@@ -105,10 +120,11 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
 #endif
           for (int j = 0; j < h.n; j++) {
             const double t = j == 0 ? h.t0 : (j == 1 ? h.t1 : (j == 2 ? h.t2 : h.t3));
-            if (t != t) { if (chain_ok(S, i, ray, ok_group)) *err |= ERR_NAN; continue; }
-            if (!C.want(t, i, nd.flags)) continue;
-            if (!chain_ok(S, i, ray, ok_group)) continue;
-            C.take(t, i);
+            const bool nan = t != t;
+            if (!nan && !C.want(t, i, nd.flags)) continue;
+            if (par == -2) par = RTC_LDG(S.parent + i);
+            if (!chain_ok(S, par, ray, ok_group)) continue;
+            if (nan) *err |= ERR_NAN; else C.take(t, i);
           }
         }
         if (C.done() || S.n_bvh <= 0) return;

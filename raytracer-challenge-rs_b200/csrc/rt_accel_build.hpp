@@ -37,7 +37,15 @@ struct BvhNode {     // 128 bytes: both children's boxes in one fetch
   int32_t _pad[4];
 };
 
+struct PrimRec {     // 128 bytes: everything the every-ray loop needs about one prim, in one place
+  int32_t node, kind, aux, parent;
+  uint32_t flags;
+  int32_t _pad[3];
+  double inv[12];    // rows 0..2 of the leaf's transform_inverse (unused for a CSG prim)
+};
+
 struct AccelBuild {
+  std::vector<PrimRec> recs;       // one per always-prim, same order as prims[0, n_always)
   std::vector<int32_t> parent;     // per node: innermost enclosing Group node (outside CSGs), or -1
   std::vector<int32_t> prims;      // node indices: [0, n_always) tested for every ray (ascending), then BVH leaf order
   int32_t n_always = 0;
@@ -272,6 +280,18 @@ struct Builder {
 
 constexpr int BVH_MIN_PRIMS = 8;  // fewer BVH-eligible prims than this: test them all, no BVH
 
+inline void fill_recs(const rtc_scene_desc* d, AccelBuild& A) {
+  A.recs.assign((size_t)A.n_always, PrimRec{});
+  for (int32_t k = 0; k < A.n_always; k++) {
+    const int32_t i = A.prims[(size_t)k];
+    const rtc_node& nd = d->nodes[i];
+    PrimRec& r = A.recs[(size_t)k];
+    r.node = i; r.kind = nd.kind; r.aux = nd.aux; r.parent = A.parent[(size_t)i]; r.flags = nd.flags;
+    if (nd.kind != RTC_CSG)
+      for (int c = 0; c < 12; c++) r.inv[c] = d->xforms[12 * (size_t)nd.xform + c];
+  }
+}
+
 // `d` must already be structurally valid (rtc_api.cu validate()).
 inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
   using namespace accel_detail;
@@ -310,9 +330,11 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
     for (auto& p : cand) A.prims.push_back(p.node);
     std::sort(A.prims.begin(), A.prims.end());
     A.n_always = (int32_t)A.prims.size();
+    fill_recs(d, A);
     return;
   }
   A.n_always = (int32_t)A.prims.size();
+  fill_recs(d, A);
   Builder b(cand, A);
   b.build();
 }

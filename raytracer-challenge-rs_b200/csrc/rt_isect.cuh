@@ -28,6 +28,7 @@ struct SceneView {
   const int32_t* parent;     // per node: innermost enclosing reference Group (outside CSGs), or -1
   const int32_t* prims;      // node indices: [0, n_always) tested for every ray, then BVH leaf order
   const BvhNode* bvh;        // binary BVH, node 0 = root
+  const PrimRec* recs;       // one record per always-prim
   int32_t n_nodes;
   int32_t n_lights;
   int32_t has_csg;

@@ -7,9 +7,6 @@
 
 #include "rt_shade.cuh"
 
-#ifndef RTK_REFILL_MIN
-#define RTK_REFILL_MIN 16
-#endif
 #ifndef RTK_MIN_BLOCKS
 #define RTK_MIN_BLOCKS 3
 #endif
@@ -47,109 +44,31 @@ __device__ __forceinline__ void flush_counters(const RayCounters& rc, uint32_t e
   }
 }
 
-// Camera::render / render_multithreaded as a PERSISTENT kernel. Work item = one pixel of the launch
-// domain (this rank's row tiles), numbered tile-major over 8x4 warp tiles so that the 32 items a
-// warp starts with are one 8x4 patch. Every warp keeps pulling items: whenever lanes finish their
-// pixel (a primary ray that misses finishes after 1 query, a glass pixel after ~60) the warp
-// re-fills exactly those lanes from its current batch (WORK_BATCH items taken from one global
-// counter), so no lane idles while others recurse — and because the whole recursion is a state
-// machine around one search site (Tracer), lanes in any phase of any pixel execute that search
-// together. counters[6] is the work counter (zeroed by the host before the launch).
-constexpr uint32_t WORK_BATCH = 128;
-
+// Camera::render / render_multithreaded: one thread per pixel (all its AA samples, summed in the
+// reference's order). 16x8 tile per CTA; warp w → 8x4 patch (w&1, w>>1); lane → (lane&7, lane>>3),
+// so the lanes of a warp put near-identical queries to the scene and stay in the same phase of the
+// Tracer state machine. (A persistent variant with lane-level re-fill was measured and rejected:
+// profiles/r01b_experiment_persistent_refill.md.)
 template <bool HAS_CSG, bool FAITHFUL>
 __global__ void __launch_bounds__(128, RTK_MIN_BLOCKS) render_kernel(SceneView S, CameraD cam, RenderParams P, double* __restrict__ out,
                                                                      unsigned long long* __restrict__ counters) {
-  const uint32_t lane = threadIdx.x & 31u;
-  const uint32_t FULL = 0xffffffffu;
-  const uint32_t tiles_x = (cam.hsize + 7u) / 8u, tiles_y = (P.owned_rows + 3u) / 4u;
-  const uint32_t n_items = tiles_x * tiles_y * 32u;
-  uint32_t next = 0, end = 0;  // the warp's batch [next, end) — warp-uniform
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  const uint32_t px = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
+  const uint32_t oy = blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
+  if (px >= cam.hsize || oy >= P.owned_rows) return;
+  // owned row index → frame row: tile (rank + k*nranks), row within tile
+  const uint32_t k = oy / P.tile_rows, r = oy - k * P.tile_rows;
+  const uint32_t py = (P.rank + k * P.nranks) * P.tile_rows + r;
+  if (py < P.row_begin || py >= P.row_end) return;
+
   Scratch<HAS_CSG> scratch;
-  Tracer tr;
-  Frame frames[MAX_FRAMES];
   RayCounters rc = {0u, 0u, 0u, 0u};
   uint32_t err = 0;
-  bool busy = false, exhausted = false;
-  uint32_t px = 0, py = 0, sample = 0;
-  V3 acc = v3(0.0, 0.0, 0.0);
-  for (;;) {
-    // ---- re-fill idle lanes ---------------------------------------------------------------------
-    // Re-fill in bulk: lanes that start together stay in phase with each other (same state-machine
-    // branch), so wait until RTK_REFILL_MIN lanes are idle — or nothing is running at all.
-    bool want = !busy && !exhausted;
-    unsigned need = __ballot_sync(FULL, want);
-    if (need && __popc(need) < RTK_REFILL_MIN && __any_sync(FULL, busy)) { need = 0; want = false; }
-    if (need) {
-      const uint32_t cnt = __popc(need), rank = __popc(need & ((1u << lane) - 1u));
-      uint32_t idx = next + rank;
-      if (next + cnt > end) {
-        unsigned long long base64 = 0;
-        if (lane == 0) base64 = atomicAdd(counters + 6, (unsigned long long)WORK_BATCH);
-        base64 = __shfl_sync(FULL, base64, 0);
-        const uint32_t base = base64 > 0xffffff00ull ? 0xffffff00u : (uint32_t)base64;
-        if (idx >= end) idx = base + (idx - end);
-        next = base + (next + cnt - end);
-        end = base + WORK_BATCH;
-      } else {
-        next += cnt;
-      }
-      if (want) {
-        if (idx >= n_items) {
-          exhausted = true;
-        } else {
-          const uint32_t tile = idx >> 5, in = idx & 31u;
-          const uint32_t ty = tile / tiles_x, tx = tile - ty * tiles_x;
-          px = tx * 8u + (in & 7u);
-          const uint32_t oy = ty * 4u + (in >> 3);
-          // owned row index → frame row: tile (rank + k*nranks), row within tile
-          const uint32_t k = oy / P.tile_rows, r = oy - k * P.tile_rows;
-          py = (P.rank + k * P.nranks) * P.tile_rows + r;
-          if (px < cam.hsize && oy < P.owned_rows && py >= P.row_begin && py < P.row_end) {
-            busy = true;
-            sample = 0;
-            acc = v3(0.0, 0.0, 0.0);
-            double ox = 0.5, oy2 = 0.5;
-            if (P.average) aa_offset(P.aa, 0, ox, oy2);
-            rc.primary++;
-            tr.start(ray_for_pixel(cam, px, py, ox, oy2), P.max_depth, &err);
-          }
-        }
-      }
-    }
-    if (!__any_sync(FULL, busy)) {
-      if (__all_sync(FULL, exhausted)) break;
-      continue;
-    }
-    // ---- one query of the state machine ---------------------------------------------------------
-    if (busy) {
-      search<HAS_CSG, FAITHFUL>(S, tr.qray, tr.q, scratch.csg(), &scratch.bvh, &err);
-      if (tr.advance(S, frames, scratch.neg, rc, &err)) {
-        V3 c = tr.result;
-        bool store = true;
-        if (P.average) {  // Color::average: sequential sum, then * (1.0/n)  (color.rs:26-33)
-          acc = acc + c;
-          sample++;
-          if (sample < P.aa) {
-            double ox, oy2;
-            aa_offset(P.aa, sample, ox, oy2);
-            rc.primary++;
-            tr.start(ray_for_pixel(cam, px, py, ox, oy2), P.max_depth, &err);
-            store = false;
-          } else {
-            c = acc * (1.0 / (double)P.aa);
-          }
-        }
-        if (store) {
-          double* o = out + ((size_t)py * cam.hsize + px) * 3;  // Canvas::pixel_idx, canvas.rs:44-48
-          o[0] = c.x;
-          o[1] = c.y;
-          o[2] = c.z;
-          busy = false;
-        }
-      }
-    }
-  }
+  V3 c = render_pixel<HAS_CSG, FAITHFUL>(S, cam, px, py, P.aa, P.average != 0, P.max_depth, scratch, rc, &err);
+  double* o = out + ((size_t)py * cam.hsize + px) * 3;  // Canvas::pixel_idx, canvas.rs:44-48
+  o[0] = c.x;
+  o[1] = c.y;
+  o[2] = c.z;
   flush_counters(rc, err, counters);
 }
 

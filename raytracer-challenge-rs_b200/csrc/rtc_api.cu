@@ -45,7 +45,6 @@ struct rtc_scene {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   uint32_t launches = 0;
-  int resident_ctas = 148 * 3;  // SMs x resident CTAs of the render kernel (occupancy query)
 };
 
 struct rtc_canvas {
@@ -169,11 +168,7 @@ int make_params(const rtc_camera* c, const rtc_opts* o, RenderParams& P, bool& f
 
 int launch_frame(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool faithful, double* out, cudaStream_t stream) {
   CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, N_COUNTERS * sizeof(unsigned long long), stream));
-  // persistent kernel: as many CTAs as are resident at once (or fewer for tiny frames)
-  const unsigned tiles = ((cam.hsize + 7) / 8) * ((P.owned_rows + 3) / 4);
-  unsigned want_ctas = (tiles + 3) / 4;
-  if (want_ctas > (unsigned)s->resident_ctas) want_ctas = (unsigned)s->resident_ctas;
-  dim3 block(128), grid(want_ctas, want_ctas ? 1 : 0);
+  dim3 block(128), grid((cam.hsize + 15) / 16, (P.owned_rows + 7) / 8);
   CUDA_TRY(cudaEventRecord(s->ev0, stream));
   if (grid.x > 0 && grid.y > 0) {
     RenderParams Pk = P;
@@ -217,9 +212,9 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   AccelBuild accel;
   build_accel(d, accel);
   // one slab: [nodes | xforms | boxes | limits | tri_geom | tri_normals | materials | patterns | lights | csg_parent
-  //            | parent | prims | bvh]
+  //            | parent | prims | bvh | recs]
   struct Part { const void* src; size_t bytes; size_t off; };
-  Part parts[13] = {
+  Part parts[14] = {
       {d->nodes, sizeof(rtc_node) * d->n_nodes, 0},
       {d->xforms, sizeof(double) * 12 * d->n_xforms, 0},
       {d->boxes, sizeof(double) * 6 * d->n_boxes, 0},
@@ -232,7 +227,8 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
       {csg_parent.data(), sizeof(int32_t) * csg_parent.size(), 0},
       {accel.parent.data(), sizeof(int32_t) * accel.parent.size(), 0},
       {accel.prims.data(), sizeof(int32_t) * accel.prims.size(), 0},
-      {accel.bvh.data(), sizeof(BvhNode) * accel.bvh.size(), 0}};
+      {accel.bvh.data(), sizeof(BvhNode) * accel.bvh.size(), 0},
+      {accel.recs.data(), sizeof(PrimRec) * accel.recs.size(), 0}};
   size_t total = 0;
   for (auto& p : parts) {
     if (p.bytes && !p.src) return fail(RTC_ERR_INVALID, "a non-empty table has a NULL pointer");
@@ -262,16 +258,6 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
     if (p.bytes) std::memcpy(stage.data() + p.off, p.src, p.bytes);
   if ((e = cudaMemcpyAsync(s->slab, stage.data(), total, cudaMemcpyHostToDevice, s->stream)) != cudaSuccess) return bail(e, "cudaMemcpy(scene)");
   if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return bail(e, "cudaStreamSynchronize");
-  {
-    cudaDeviceProp prop;
-    int per_sm = 0;
-    cudaError_t oe = has_csg ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_kernel<true, false>, 128, 0)
-                             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_kernel<false, false>, 128, 0);
-    if (oe == cudaSuccess && per_sm > 0 && cudaGetDeviceProperties(&prop, device) == cudaSuccess)
-      s->resident_ctas = per_sm * prop.multiProcessorCount;
-    else
-      cudaGetLastError();
-  }
   SceneView& v = s->view;
   v.nodes = (const rtc_node*)(s->slab + parts[0].off);
   v.xforms = (const double*)(s->slab + parts[1].off);
@@ -286,6 +272,7 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   v.parent = (const int32_t*)(s->slab + parts[10].off);
   v.prims = (const int32_t*)(s->slab + parts[11].off);
   v.bvh = (const BvhNode*)(s->slab + parts[12].off);
+  v.recs = (const PrimRec*)(s->slab + parts[13].off);
   v.n_always = accel.n_always;
   v.n_bvh = (int32_t)accel.bvh.size();
   v.n_nodes = (int32_t)d->n_nodes;
