@@ -29,6 +29,13 @@ extern "C" {
 
 #define RTC_ABI_VERSION 1
 
+/* Only the entry points below are exported; everything else in the library has hidden visibility. */
+#if defined(__GNUC__)
+#define RTC_API __attribute__((visibility("default")))
+#else
+#define RTC_API
+#endif
+
 typedef enum rtc_status {
   RTC_OK = 0,
   RTC_ERR_INVALID = -1,   /* malformed description / argument */
@@ -150,62 +157,62 @@ typedef struct rtc_stats {
 
 typedef struct rtc_scene rtc_scene;
 
-const char* rtc_last_error(void);
-int rtc_abi_version(void);
-int rtc_device_count(void);
+RTC_API const char* rtc_last_error(void);
+RTC_API int rtc_abi_version(void);
+RTC_API int rtc_device_count(void);
 
 /* Upload a flattened world to `device`. Replaces building `World` (world.rs:24,83-93). */
-int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out);
-void rtc_scene_destroy(rtc_scene* scene);
+RTC_API int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out);
+RTC_API void rtc_scene_destroy(rtc_scene* scene);
 
 /* Camera::render / render_multithreaded (camera.rs:133,150): render into a HOST canvas of
  * hsize*vsize*3 doubles, row-major y*hsize+x like Canvas (canvas.rs:44-48). The device→host copy
  * of the rendered rows is part of the call. */
-int rtc_render(rtc_scene* scene, const rtc_camera* camera, const rtc_opts* opts, double* rgb_host,
+RTC_API int rtc_render(rtc_scene* scene, const rtc_camera* camera, const rtc_opts* opts, double* rgb_host,
                rtc_stats* stats);
 
 /* Same, into a DEVICE canvas (same layout; may be a peer-mapped pointer on another GPU — the
  * multi-GPU gather is the kernel's own stores over NVLink). Asynchronous on `stream`
  * (a cudaStream_t, NULL = default stream) unless `stats` is non-NULL, in which case the call
  * synchronises the stream to fill it. */
-int rtc_render_device(rtc_scene* scene, const rtc_camera* camera, const rtc_opts* opts, double* rgb_dev,
+RTC_API int rtc_render_device(rtc_scene* scene, const rtc_camera* camera, const rtc_opts* opts, double* rgb_dev,
                       void* stream, rtc_stats* stats);
 
 /* Wait for the work queued on `stream` by rtc_render_device(…, stats = NULL), check the device
  * error flags and fill `stats` (ray counts; kernel_ms of the last launch). */
-int rtc_scene_finish(rtc_scene* scene, void* stream, rtc_stats* stats);
+RTC_API int rtc_scene_finish(rtc_scene* scene, void* stream, rtc_stats* stats);
 
 /* Output stage (image/ppm.rs:73-75, png.rs:29-31): rgb8 = (v*255).round() as u8, saturating,
  * NaN→0, for n doubles already on the device → n bytes on the device. */
-int rtc_quantize_device(int device, const double* rgb_dev, size_t n, uint8_t* rgb8_dev, void* stream);
+RTC_API int rtc_quantize_device(int device, const double* rgb_dev, size_t n, uint8_t* rgb8_dev, void* stream);
 
 /* Debug / known-answer entry: World::color_at(ray, remaining) (world.rs:70) for a batch of HOST
  * rays. rgb_out (3n) and t_out (n; hit t or -1) may each be NULL. */
-int rtc_trace_rays(rtc_scene* scene, size_t n, const double* origins, const double* directions,
+RTC_API int rtc_trace_rays(rtc_scene* scene, size_t n, const double* origins, const double* directions,
                    uint32_t remaining, double* rgb_out, double* t_out);
 
 /* Debug / known-answer entry: Intersection::prepare_computations (geometry/intersection.rs:53)
  * for one host ray. out[20] = hit(0/1), t, point[3], normalv[3], over_point[3], under_point[3],
  * reflectv[3], n1, n2, inside. */
-int rtc_probe_hit(rtc_scene* scene, const double* origin, const double* direction, double* out20);
+RTC_API int rtc_probe_hit(rtc_scene* scene, const double* origin, const double* direction, double* out20);
 
 /* Debug / known-answer entry: World::is_shadowed(point, light) (world.rs:95). Returns 0/1 or <0. */
-int rtc_is_shadowed(rtc_scene* scene, const double* point, uint32_t light_index);
+RTC_API int rtc_is_shadowed(rtc_scene* scene, const double* point, uint32_t light_index);
 
 /* Device canvases for the multi-GPU gather: rank 0 creates one, exports its CUDA IPC handle
  * (64 bytes), the other ranks open it and pass rtc_canvas_ptr() to rtc_render_device. */
 typedef struct rtc_canvas rtc_canvas;
-int rtc_canvas_create(int device, size_t n_doubles, rtc_canvas** out);
-int rtc_canvas_export(rtc_canvas* canvas, unsigned char handle[64]);
-int rtc_canvas_open(int device, const unsigned char handle[64], size_t n_doubles, rtc_canvas** out);
-double* rtc_canvas_ptr(rtc_canvas* canvas);
-int rtc_canvas_download(rtc_canvas* canvas, double* host, size_t offset_doubles, size_t n_doubles);
-void rtc_canvas_destroy(rtc_canvas* canvas);
+RTC_API int rtc_canvas_create(int device, size_t n_doubles, rtc_canvas** out);
+RTC_API int rtc_canvas_export(rtc_canvas* canvas, unsigned char handle[64]);
+RTC_API int rtc_canvas_open(int device, const unsigned char handle[64], size_t n_doubles, rtc_canvas** out);
+RTC_API double* rtc_canvas_ptr(rtc_canvas* canvas);
+RTC_API int rtc_canvas_download(rtc_canvas* canvas, double* host, size_t offset_doubles, size_t n_doubles);
+RTC_API void rtc_canvas_destroy(rtc_canvas* canvas);
 
 /* Roofline denominator: measured FP64 throughput of `device` in GFLOP/s.
  * fused=1: dependent-chain-free DFMA stream (2 flops each); fused=0: alternating DADD/DMUL
  * (1 flop each) — the attainable roof for this library, which is built with --fmad=false. */
-int rtc_measure_fp64(int device, int fused, double* gflops_out);
+RTC_API int rtc_measure_fp64(int device, int fused, double* gflops_out);
 
 #ifdef __cplusplus
 }

@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "--fmad=false", "-std=c++17",
-              "-Xcompiler", "-fPIC,-ffp-contract=off", "-shared"]
+              "-Xcompiler", "-fPIC,-ffp-contract=off,-fvisibility=hidden", "-shared"]
 GXX_FLAGS = ["-O2", "-std=c++17", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-Wall", "-Wextra", "-pthread"]
 
 
@@ -76,7 +76,8 @@ def build_emul(force=False):
     out = os.path.join(d, "libemul.so")
     srcs = [os.path.join(d, "emul.cpp")] + _glob(os.path.join(HERE, "csrc"), (".cuh",)) + [os.path.join(ROOT, "include", "rtc.h")]
     if force or _newer(out, srcs):
-        _run(["g++"] + GXX_FLAGS + ["-shared", "-o", out, os.path.join(d, "emul.cpp")])
+        # hidden visibility + -Bsymbolic: the inline rtk:: helpers it shares with librtc_cuda.so must not interpose
+        _run(["g++"] + GXX_FLAGS + ["-fvisibility=hidden", "-Wl,-Bsymbolic", "-shared", "-o", out, os.path.join(d, "emul.cpp")])
     return out
 
 

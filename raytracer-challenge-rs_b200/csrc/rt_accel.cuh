@@ -61,6 +61,18 @@ RTC_HD bool own_box(const double* lo, const double* hi, const RayD& r, V3 inv, d
   return tmin <= tmax + 1e-9 * (fabs(tmin) + fabs(tmax));
 }
 
+// Lazy division. t = num/den (den > 0) is only worth an IEEE division (≈ a dozen FP64-pipe
+// instructions) if the query could want it. These pre-filters never reject a t the query would
+// take: the sign of the quotient is the sign of num (magnitudes kept away from underflow, where
+// -tiny/den could round to -0.0, which `t >= 0.0` accepts), and num > limit·den·(1+1e-9) puts the
+// correctly rounded quotient strictly beyond the limit (the tie t == limit is never filtered).
+RTC_HD bool quot_unwanted(const Query& C, double num, double den) {
+  if (!(den > 0.0) || !(den < 1e150)) return false;
+  if (C.mode == Q_NEG) return num > 1e-150;
+  if (num < -1e-150) return true;
+  return num > C.limit * den * (1.0 + 1e-9);
+}
+
 // World::intersect → query. FAITHFUL: the reference's own search order, node by node (walk_range
 // over the whole array). Otherwise: the prims tested for every ray, then the BVH; ONE leaf-test
 // site and ONE candidate site serve both, so the hot loop stays small.
@@ -78,8 +90,61 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
     V3 inv = v3(0.0, 0.0, 0.0);
     bool have_inv = false;
     int sp = 0;
+    // one candidate intersection: want → validate against the reference's group chain → take
+    auto cand = [&](double t, int32_t i, uint32_t flags, int32_t par) {
+      const bool nan = t != t;
+      if (!nan && !C.want(t, i, flags)) return;
+      if (par != ok_group && !chain_ok(S, par, ray, ok_group)) return;
+      if (nan) *err |= ERR_NAN; else C.take(t, i);
+    };
+    // ---- every-ray spheres (sphere.rs:47-62): switch-free, divisions only for wanted roots ---------
+    int32_t k0 = 0;
+    for (; k0 < S.n_sph && !C.done(); k0++) {
+      const PrimRec* rec = S.recs + k0;
+      RTK_COUNT(prim_tests, 1);
+#if defined(__CUDA_ARCH__)
+      const int4 hd = __ldg(reinterpret_cast<const int4*>(rec));
+      const int32_t i = hd.x, par = hd.w;
+#else
+      const int32_t i = rec->node, par = rec->parent;
+#endif
+      const uint32_t flags = RTC_LDG(&rec->flags);
+      const RayD r = ray_transform_v2(rec->inv, ray);
+      const double a = dot(r.d, r.d);
+      const double b = 2.0 * dot(r.d, r.o);
+      const double c = dot(r.o, r.o) - 1.0;
+      const double disc = b * b - 4.0 * a * c;
+      if (disc < 0.0) continue;
+      const double sq = sqrt(disc);
+      const double a2 = 2.0 * a, num1 = -b - sq, num2 = -b + sq;
+      if (!quot_unwanted(C, num1, a2)) cand(num1 / a2, i, flags, par);
+      if (!quot_unwanted(C, num2, a2)) cand(num2 / a2, i, flags, par);
+    }
+    // ---- every-ray planes (plane.rs:53-60): only row 1 of the inverse is needed --------------------
+    for (; k0 < S.n_sph + S.n_pl && !C.done(); k0++) {
+      const PrimRec* rec = S.recs + k0;
+      RTK_COUNT(prim_tests, 1);
+#if defined(__CUDA_ARCH__)
+      const int4 hd = __ldg(reinterpret_cast<const int4*>(rec));
+      const int32_t i = hd.x, par = hd.w;
+      const double2 m45 = __ldg(reinterpret_cast<const double2*>(rec->inv + 4));
+      const double2 m67 = __ldg(reinterpret_cast<const double2*>(rec->inv + 6));
+      const double m4 = m45.x, m5 = m45.y, m6 = m67.x, m7 = m67.y;
+#else
+      const int32_t i = rec->node, par = rec->parent;
+      const double m4 = rec->inv[4], m5 = rec->inv[5], m6 = rec->inv[6], m7 = rec->inv[7];
+#endif
+      const uint32_t flags = RTC_LDG(&rec->flags);
+      const double oy = m4 * ray.o.x + m5 * ray.o.y + m6 * ray.o.z + m7;  // matrix.rs:240, row 1
+      const double dy = m4 * ray.d.x + m5 * ray.d.y + m6 * ray.d.z;       // matrix.rs:255, row 1
+      if (fabs(dy) < EPS) continue;
+      const bool neg = dy < 0.0;
+      if (quot_unwanted(C, neg ? oy : -oy, neg ? -dy : dy)) continue;
+      cand(-oy / dy, i, flags, par);
+    }
     // current item: a run of prims [first, first+count) (leaf) or a BVH node (cur >= 0)
-    int32_t first = 0, count = S.n_always, cur = -1;
+    int32_t first = k0, count = S.n_always - k0, cur = -1;
+    if (C.done()) return;
     for (;;) {
       if (cur < 0) {
         for (int32_t k = first; k < first + count && !C.done(); k++) {
@@ -120,11 +185,8 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
 #endif
           for (int j = 0; j < h.n; j++) {
             const double t = j == 0 ? h.t0 : (j == 1 ? h.t1 : (j == 2 ? h.t2 : h.t3));
-            const bool nan = t != t;
-            if (!nan && !C.want(t, i, nd.flags)) continue;
-            if (par == -2) par = RTC_LDG(S.parent + i);
-            if (!chain_ok(S, par, ray, ok_group)) continue;
-            if (nan) *err |= ERR_NAN; else C.take(t, i);
+            if (par == -2 && (t != t || C.want(t, i, nd.flags))) par = RTC_LDG(S.parent + i);
+            cand(t, i, nd.flags, par);
           }
         }
         if (C.done() || S.n_bvh <= 0) return;

@@ -49,6 +49,7 @@ struct AccelBuild {
   std::vector<int32_t> parent;     // per node: innermost enclosing Group node (outside CSGs), or -1
   std::vector<int32_t> prims;      // node indices: [0, n_always) tested for every ray (ascending), then BVH leaf order
   int32_t n_always = 0;
+  int32_t n_sph = 0, n_pl = 0;     // the always-prefix is ordered spheres, planes, everything else
   std::vector<BvhNode> bvh;        // node 0 = root (empty vector: no BVH)
   int32_t max_depth = 0;
 };
@@ -281,6 +282,15 @@ struct Builder {
 constexpr int BVH_MIN_PRIMS = 8;  // fewer BVH-eligible prims than this: test them all, no BVH
 
 inline void fill_recs(const rtc_scene_desc* d, AccelBuild& A) {
+  // kind-sorted so the every-ray loop runs one tight, switch-free loop per common kind; the order
+  // of evaluation is free because ties in t resolve by node index, not by arrival
+  auto cls = [&](int32_t i) { int k = d->nodes[i].kind; return k == RTC_SPHERE ? 0 : (k == RTC_PLANE ? 1 : 2); };
+  std::stable_sort(A.prims.begin(), A.prims.begin() + A.n_always, [&](int32_t x, int32_t y) { return cls(x) < cls(y); });
+  A.n_sph = A.n_pl = 0;
+  for (int32_t k = 0; k < A.n_always; k++) {
+    int c = cls(A.prims[(size_t)k]);
+    if (c == 0) A.n_sph++; else if (c == 1) A.n_pl++;
+  }
   A.recs.assign((size_t)A.n_always, PrimRec{});
   for (int32_t k = 0; k < A.n_always; k++) {
     const int32_t i = A.prims[(size_t)k];

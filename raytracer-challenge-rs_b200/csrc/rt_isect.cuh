@@ -34,6 +34,7 @@ struct SceneView {
   int32_t has_csg;
   int32_t n_always;
   int32_t n_bvh;             // BVH node count (0: no BVH)
+  int32_t n_sph, n_pl;       // always-prefix: [0,n_sph) spheres, [n_sph,n_sph+n_pl) planes, then the rest
   int32_t _pad;
 };
 

@@ -260,10 +260,13 @@ struct Tracer {
   RayD ray;        // the ray color_at is being evaluated for (current recursion level)
   RayD qray;       // the ray of the pending query
   Query q;
-  Comps c;         // the hit being shaded (live across its shadow / containers queries)
-  MatD m;
+  // the hit being shaded, live across its shadow / containers queries — kept minimal (registers):
+  // eyev = -ray.d, under_point, reflectv and the material scalars are re-derived bit-identically
+  // when they are needed instead of being carried through every search
+  V3 point, over_point, normalv;
   V3 color, surface, result;
   double t_primary;
+  int32_t node, mat;
   int sp, remaining, li, phase;
   bool want_reflect, want_refract;
 
@@ -275,9 +278,9 @@ struct Tracer {
     li = 0;
     phase = PH_CLOSEST;
     want_reflect = want_refract = false;
-    result = v3(0.0, 0.0, 0.0);
     t_primary = -1.0;
-    c.node = -1;
+    node = -1;
+    mat = 0;
     q.init_closest(err);
   }
 
@@ -285,17 +288,27 @@ struct Tracer {
   // primary ray is complete (`result`).
   RTC_HD bool advance(const SceneView& S, Frame* frames, HitList& neg, RayCounters& rc, uint32_t* err) {
     int next;
+    V3 res = v3(0.0, 0.0, 0.0);
+    double n1 = -1.0, n2 = -1.0;
     if (phase == PH_CLOSEST) {
       if (sp == 0) t_primary = q.node >= 0 ? q.limit : -1.0;
       if (q.node < 0) {
-        result = v3(0.0, 0.0, 0.0);  // Color::black()
+        res = v3(0.0, 0.0, 0.0);  // Color::black()
         next = NX_RETURN;
       } else {
         rtc_node nd = load_node(S.nodes + q.node);
-        m = load_material(S, nd.material);
+        Comps c;
         prepare(S, ray, q.limit, q.node, nd, c);
+        point = c.point;
+        over_point = c.over_point;
+        normalv = c.normalv;
+        node = q.node;
+        mat = nd.material;
+        const rtc_material* M = S.materials + mat;
+        const int32_t pat = RTC_LDG(&M->pattern);
         const double* leaf_inv = S.xforms + 12 * (size_t)nd.xform;
-        color = m.pattern >= 0 ? pattern_color(S, m.pattern, leaf_inv, c.over_point) : m.color;
+        color = pat >= 0 ? pattern_color(S, pat, leaf_inv, over_point)
+                         : v3(RTC_LDG(&M->color[0]), RTC_LDG(&M->color[1]), RTC_LDG(&M->color[2]));
         surface = v3(0.0, 0.0, 0.0);  // shade_hit: Σ lighting in light order from (0,0,0), world.rs:41-58
         li = 0;
         next = S.n_lights > 0 ? NX_SHADOW : NX_LIT;
@@ -304,19 +317,20 @@ struct Tracer {
       const rtc_light* L = S.lights + li;
       V3 lp = v3(RTC_LDG(&L->position[0]), RTC_LDG(&L->position[1]), RTC_LDG(&L->position[2]));
       V3 lint = v3(RTC_LDG(&L->intensity[0]), RTC_LDG(&L->intensity[1]), RTC_LDG(&L->intensity[2]));
-      surface = surface + lighting(m, color, lp, lint, c.over_point, c.eyev, c.normalv, q.done());
+      const MatD m = load_material(S, mat);
+      surface = surface + lighting(m, color, lp, lint, over_point, -ray.d, normalv, q.done());
       li++;
       next = li < S.n_lights ? NX_SHADOW : NX_LIT;
     } else {
-      containers_n1n2(S, neg, c.node, c.n1, c.n2, err);
+      containers_n1n2(S, neg, node, n1, n2, err);
       next = NX_N1N2;
     }
     if (next == NX_SHADOW) {  // World::is_shadowed(over_point, light li), world.rs:95-105
       const rtc_light* L = S.lights + li;
       V3 lp = v3(RTC_LDG(&L->position[0]), RTC_LDG(&L->position[1]), RTC_LDG(&L->position[2]));
-      V3 v = lp - c.over_point;
+      V3 v = lp - over_point;
       double distance = magnitude(v);
-      qray.o = c.over_point;
+      qray.o = over_point;
       qray.d = normalize(v);
       q.init_shadow(distance, err);
       rc.shadow++;
@@ -326,12 +340,14 @@ struct Tracer {
     bool descend = false;
     if (next == NX_LIT) {
       Frame& f = frames[sp];
+      const rtc_material* M = S.materials + mat;
+      const double reflective = RTC_LDG(&M->reflective), transparency = RTC_LDG(&M->transparency);
       f.surface = surface;
-      f.reflective = m.reflective;
-      f.transparency = m.transparency;
-      want_reflect = !(feq(m.reflective, 0.0) || remaining == 0);    // world.rs:108
-      want_refract = !(feq(m.transparency, 0.0) || remaining == 0);  // world.rs:117
-      f.use_schlick = (m.reflective > 0.0 && m.transparency > 0.0) ? 1 : 0;  // world.rs:62
+      f.reflective = reflective;
+      f.transparency = transparency;
+      want_reflect = !(feq(reflective, 0.0) || remaining == 0);    // world.rs:108
+      want_refract = !(feq(transparency, 0.0) || remaining == 0);  // world.rs:117
+      f.use_schlick = (reflective > 0.0 && transparency > 0.0) ? 1 : 0;  // world.rs:62
       f.need_refract = 0;
       f.reflectance = 0.0;
       if (want_refract || f.use_schlick) {
@@ -345,23 +361,29 @@ struct Tracer {
     }
     if (next == NX_N1N2) {
       Frame& f = frames[sp];
-      if (f.use_schlick) f.reflectance = schlick(c);
+      const V3 eyev = -ray.d;
+      if (f.use_schlick) {
+        Comps c;
+        c.eyev = eyev; c.normalv = normalv; c.n1 = n1; c.n2 = n2;
+        f.reflectance = schlick(c);
+      }
       if (want_refract) {  // world.rs:121-131
-        double n_ratio = c.n1 / c.n2;
-        double cos_i = dot(c.eyev, c.normalv);
+        double n_ratio = n1 / n2;
+        double cos_i = dot(eyev, normalv);
         double sin2_t = n_ratio * n_ratio * (1.0 - cos_i * cos_i);
         if (!(sin2_t > 1.0)) {
           double cos_t = sqrt(1.0 - sin2_t);
-          f.refr_ray.o = c.under_point;
-          f.refr_ray.d = c.normalv * (n_ratio * cos_i - cos_t) - c.eyev * n_ratio;  // not normalised
+          f.refr_ray.o = point - normalv * EPS;  // under_point, intersection.rs:99
+          f.refr_ray.d = normalv * (n_ratio * cos_i - cos_t) - eyev * n_ratio;  // not normalised
           f.need_refract = 1;
         }
       }
       if (want_reflect) {
         rc.reflect++;
         f.state = 1;
-        ray.o = c.over_point;
-        ray.d = c.reflectv;
+        const V3 reflectv = reflect(ray.d, normalv);  // intersection.rs:100
+        ray.o = over_point;
+        ray.d = reflectv;
         descend = true;
       } else {
         f.reflected = v3(0.0, 0.0, 0.0);
@@ -371,28 +393,28 @@ struct Tracer {
           ray = f.refr_ray;
           descend = true;
         } else {
-          result = combine(f, v3(0.0, 0.0, 0.0));
+          res = combine(f, v3(0.0, 0.0, 0.0));
         }
       }
     }
-    // ---- return `result` to the parents -----------------------------------------------------------
+    // ---- return `res` to the parents --------------------------------------------------------------
     while (!descend) {
-      if (sp == 0) return true;
+      if (sp == 0) { result = res; return true; }
       sp--;
       remaining++;
       Frame& f = frames[sp];
       if (f.state == 1) {
-        f.reflected = result * f.reflective;  // world.rs:113
+        f.reflected = res * f.reflective;  // world.rs:113
         if (f.need_refract) {
           rc.refract++;
           f.state = 2;
           ray = f.refr_ray;
           descend = true;
         } else {
-          result = combine(f, v3(0.0, 0.0, 0.0));
+          res = combine(f, v3(0.0, 0.0, 0.0));
         }
       } else {
-        result = combine(f, result * f.transparency);  // world.rs:133
+        res = combine(f, res * f.transparency);  // world.rs:133
       }
     }
     sp++;

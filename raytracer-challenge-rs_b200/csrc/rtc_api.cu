@@ -274,6 +274,8 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   v.bvh = (const BvhNode*)(s->slab + parts[12].off);
   v.recs = (const PrimRec*)(s->slab + parts[13].off);
   v.n_always = accel.n_always;
+  v.n_sph = accel.n_sph;
+  v.n_pl = accel.n_pl;
   v.n_bvh = (int32_t)accel.bvh.size();
   v.n_nodes = (int32_t)d->n_nodes;
   v.n_lights = (int32_t)d->n_lights;

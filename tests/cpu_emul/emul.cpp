@@ -39,7 +39,7 @@ void build_view(const rtc_scene_desc* d, Built& b) {
   v.n_nodes = n; v.n_lights = (int32_t)d->n_lights; v.has_csg = has_csg ? 1 : 0; v._pad = 0;
   build_accel(d, b.accel);
   v.parent = b.accel.parent.data(); v.prims = b.accel.prims.data(); v.recs = b.accel.recs.data();
-  v.bvh = b.accel.bvh.data(); v.n_always = b.accel.n_always; v.n_bvh = (int32_t)b.accel.bvh.size();
+  v.bvh = b.accel.bvh.data(); v.n_always = b.accel.n_always; v.n_sph = b.accel.n_sph; v.n_pl = b.accel.n_pl; v.n_bvh = (int32_t)b.accel.bvh.size();
 }
 CameraD make_cam(const rtc_camera* c) {
   CameraD cam;
@@ -74,11 +74,12 @@ void rows(const SceneView& S, const CameraD& cam, uint32_t y0, uint32_t y1, uint
 }
 }  // namespace
 
+#define EMUL_API __attribute__((visibility("default")))
 extern "C" {
 
 // Same meaning as rtc_render, on host threads. counters[6] = rays primary/shadow/reflect/refract,
 // overflow pixels, NaN pixels.
-int emul_render(const rtc_scene_desc* d, const rtc_camera* c, const rtc_opts* o, unsigned threads, double* rgb,
+EMUL_API int emul_render(const rtc_scene_desc* d, const rtc_camera* c, const rtc_opts* o, unsigned threads, double* rgb,
                 uint64_t* counters) {
   Built b;
   build_view(d, b);
@@ -107,7 +108,7 @@ int emul_render(const rtc_scene_desc* d, const rtc_camera* c, const rtc_opts* o,
   return 0;
 }
 
-int emul_trace_rays(const rtc_scene_desc* d, size_t n, const double* origins, const double* dirs, uint32_t remaining,
+EMUL_API int emul_trace_rays(const rtc_scene_desc* d, size_t n, const double* origins, const double* dirs, uint32_t remaining,
                     double* rgb, double* t_out) {
   Built b;
   build_view(d, b);
@@ -127,7 +128,7 @@ int emul_trace_rays(const rtc_scene_desc* d, size_t n, const double* origins, co
   return (int)err;
 }
 
-int emul_probe_hit(const rtc_scene_desc* d, const double* o, const double* dir, double* out) {
+EMUL_API int emul_probe_hit(const rtc_scene_desc* d, const double* o, const double* dir, double* out) {
   Built b;
   build_view(d, b);
   const SceneView& S = b.view;
@@ -158,7 +159,7 @@ int emul_probe_hit(const rtc_scene_desc* d, const double* o, const double* dir, 
   return (int)err;
 }
 
-int emul_is_shadowed(const rtc_scene_desc* d, const double* p, uint32_t light) {
+EMUL_API int emul_is_shadowed(const rtc_scene_desc* d, const double* p, uint32_t light) {
   Built b;
   build_view(d, b);
   uint32_t err = 0;
