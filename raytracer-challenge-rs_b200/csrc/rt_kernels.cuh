@@ -8,7 +8,7 @@
 #include "rt_shade.cuh"
 
 #ifndef RTK_MIN_BLOCKS
-#define RTK_MIN_BLOCKS 3
+#define RTK_MIN_BLOCKS 4
 #endif
 
 namespace rtk {

@@ -232,13 +232,20 @@ RTC_HD double schlick(const Comps& c) {
   return r0 + (1.0 - r0) * (x * x4);
 }
 
+// One level of the color_at recursion. Lives in LOCAL memory (dynamically indexed array): all the
+// state of the hit being shaded that is not needed INSIDE a search is parked here, so the search
+// loop runs with few live registers (more resident warps hide the FP64 latency).
 struct Frame {
+  RayD ray;        // the ray color_at is being evaluated for at this level
+  V3 point, over_point, normalv;  // of the hit being shaded (eyev = -ray.d, under_point and reflectv are re-derived)
+  V3 color;        // pattern / material colour at over_point
   V3 surface;      // Σ lights
   V3 reflected;    // reflected_color result
   RayD refr_ray;   // pending refraction ray
   double reflective, transparency, reflectance;
+  int32_t node, mat;
   uint8_t state;   // 1: waiting for reflection child, 2: waiting for refraction child
-  uint8_t need_refract, use_schlick, _pad;
+  uint8_t need_refract, use_schlick, want_reflect, want_refract, _pad[3];
 };
 
 RTC_HD V3 combine(const Frame& f, V3 refracted) {  // world.rs:62-67
@@ -257,30 +264,20 @@ enum : int { PH_CLOSEST = 0, PH_SHADOW = 1, PH_NEG = 2 };
 enum : int { NX_RETURN = 0, NX_SHADOW = 1, NX_LIT = 2, NX_N1N2 = 3 };
 
 struct Tracer {
-  RayD ray;        // the ray color_at is being evaluated for (current recursion level)
   RayD qray;       // the ray of the pending query
   Query q;
-  // the hit being shaded, live across its shadow / containers queries — kept minimal (registers):
-  // eyev = -ray.d, under_point, reflectv and the material scalars are re-derived bit-identically
-  // when they are needed instead of being carried through every search
-  V3 point, over_point, normalv;
-  V3 color, surface, result;
+  V3 result;
   double t_primary;
-  int32_t node, mat;
   int sp, remaining, li, phase;
-  bool want_reflect, want_refract;
 
-  RTC_HD void start(const RayD& r, int max_depth, uint32_t* err) {
-    ray = r;
+  RTC_HD void start(const RayD& r, int max_depth, Frame* frames, uint32_t* err) {
+    frames[0].ray = r;
     qray = r;
     sp = 0;
     remaining = max_depth;
     li = 0;
     phase = PH_CLOSEST;
-    want_reflect = want_refract = false;
     t_primary = -1.0;
-    node = -1;
-    mat = 0;
     q.init_closest(err);
   }
 
@@ -290,6 +287,7 @@ struct Tracer {
     int next;
     V3 res = v3(0.0, 0.0, 0.0);
     double n1 = -1.0, n2 = -1.0;
+    Frame& f = frames[sp];
     if (phase == PH_CLOSEST) {
       if (sp == 0) t_primary = q.node >= 0 ? q.limit : -1.0;
       if (q.node < 0) {
@@ -298,18 +296,18 @@ struct Tracer {
       } else {
         rtc_node nd = load_node(S.nodes + q.node);
         Comps c;
-        prepare(S, ray, q.limit, q.node, nd, c);
-        point = c.point;
-        over_point = c.over_point;
-        normalv = c.normalv;
-        node = q.node;
-        mat = nd.material;
-        const rtc_material* M = S.materials + mat;
+        prepare(S, f.ray, q.limit, q.node, nd, c);
+        f.point = c.point;
+        f.over_point = c.over_point;
+        f.normalv = c.normalv;
+        f.node = q.node;
+        f.mat = nd.material;
+        const rtc_material* M = S.materials + nd.material;
         const int32_t pat = RTC_LDG(&M->pattern);
         const double* leaf_inv = S.xforms + 12 * (size_t)nd.xform;
-        color = pat >= 0 ? pattern_color(S, pat, leaf_inv, over_point)
-                         : v3(RTC_LDG(&M->color[0]), RTC_LDG(&M->color[1]), RTC_LDG(&M->color[2]));
-        surface = v3(0.0, 0.0, 0.0);  // shade_hit: Σ lighting in light order from (0,0,0), world.rs:41-58
+        f.color = pat >= 0 ? pattern_color(S, pat, leaf_inv, c.over_point)
+                           : v3(RTC_LDG(&M->color[0]), RTC_LDG(&M->color[1]), RTC_LDG(&M->color[2]));
+        f.surface = v3(0.0, 0.0, 0.0);  // shade_hit: Σ lighting in light order from (0,0,0), world.rs:41-58
         li = 0;
         next = S.n_lights > 0 ? NX_SHADOW : NX_LIT;
       }
@@ -317,20 +315,21 @@ struct Tracer {
       const rtc_light* L = S.lights + li;
       V3 lp = v3(RTC_LDG(&L->position[0]), RTC_LDG(&L->position[1]), RTC_LDG(&L->position[2]));
       V3 lint = v3(RTC_LDG(&L->intensity[0]), RTC_LDG(&L->intensity[1]), RTC_LDG(&L->intensity[2]));
-      const MatD m = load_material(S, mat);
-      surface = surface + lighting(m, color, lp, lint, over_point, -ray.d, normalv, q.done());
+      const MatD m = load_material(S, f.mat);
+      f.surface = f.surface + lighting(m, f.color, lp, lint, f.over_point, -f.ray.d, f.normalv, q.done());
       li++;
       next = li < S.n_lights ? NX_SHADOW : NX_LIT;
     } else {
-      containers_n1n2(S, neg, node, n1, n2, err);
+      containers_n1n2(S, neg, f.node, n1, n2, err);
       next = NX_N1N2;
     }
     if (next == NX_SHADOW) {  // World::is_shadowed(over_point, light li), world.rs:95-105
       const rtc_light* L = S.lights + li;
       V3 lp = v3(RTC_LDG(&L->position[0]), RTC_LDG(&L->position[1]), RTC_LDG(&L->position[2]));
-      V3 v = lp - over_point;
+      const V3 op = f.over_point;
+      V3 v = lp - op;
       double distance = magnitude(v);
-      qray.o = over_point;
+      qray.o = op;
       qray.d = normalize(v);
       q.init_shadow(distance, err);
       rc.shadow++;
@@ -338,21 +337,21 @@ struct Tracer {
       return false;
     }
     bool descend = false;
+    RayD child;
+    child.o = child.d = v3(0.0, 0.0, 0.0);
     if (next == NX_LIT) {
-      Frame& f = frames[sp];
-      const rtc_material* M = S.materials + mat;
+      const rtc_material* M = S.materials + f.mat;
       const double reflective = RTC_LDG(&M->reflective), transparency = RTC_LDG(&M->transparency);
-      f.surface = surface;
       f.reflective = reflective;
       f.transparency = transparency;
-      want_reflect = !(feq(reflective, 0.0) || remaining == 0);    // world.rs:108
-      want_refract = !(feq(transparency, 0.0) || remaining == 0);  // world.rs:117
+      f.want_reflect = !(feq(reflective, 0.0) || remaining == 0);    // world.rs:108
+      f.want_refract = !(feq(transparency, 0.0) || remaining == 0);  // world.rs:117
       f.use_schlick = (reflective > 0.0 && transparency > 0.0) ? 1 : 0;  // world.rs:62
       f.need_refract = 0;
       f.reflectance = 0.0;
-      if (want_refract || f.use_schlick) {
+      if (f.want_refract || f.use_schlick) {
         // n1/n2 are only ever consumed by refracted_color and schlick
-        qray = ray;
+        qray = f.ray;
         q.init_neg(&neg, err);
         phase = PH_NEG;
         return false;
@@ -360,37 +359,36 @@ struct Tracer {
       next = NX_N1N2;
     }
     if (next == NX_N1N2) {
-      Frame& f = frames[sp];
-      const V3 eyev = -ray.d;
+      const V3 rd = f.ray.d, normalv = f.normalv;
+      const V3 eyev = -rd;
       if (f.use_schlick) {
         Comps c;
         c.eyev = eyev; c.normalv = normalv; c.n1 = n1; c.n2 = n2;
         f.reflectance = schlick(c);
       }
-      if (want_refract) {  // world.rs:121-131
+      if (f.want_refract) {  // world.rs:121-131
         double n_ratio = n1 / n2;
         double cos_i = dot(eyev, normalv);
         double sin2_t = n_ratio * n_ratio * (1.0 - cos_i * cos_i);
         if (!(sin2_t > 1.0)) {
           double cos_t = sqrt(1.0 - sin2_t);
-          f.refr_ray.o = point - normalv * EPS;  // under_point, intersection.rs:99
+          f.refr_ray.o = f.point - normalv * EPS;  // under_point, intersection.rs:99
           f.refr_ray.d = normalv * (n_ratio * cos_i - cos_t) - eyev * n_ratio;  // not normalised
           f.need_refract = 1;
         }
       }
-      if (want_reflect) {
+      if (f.want_reflect) {
         rc.reflect++;
         f.state = 1;
-        const V3 reflectv = reflect(ray.d, normalv);  // intersection.rs:100
-        ray.o = over_point;
-        ray.d = reflectv;
+        child.o = f.over_point;
+        child.d = reflect(rd, normalv);  // reflectv, intersection.rs:100
         descend = true;
       } else {
         f.reflected = v3(0.0, 0.0, 0.0);
         if (f.need_refract) {
           rc.refract++;
           f.state = 2;
-          ray = f.refr_ray;
+          child = f.refr_ray;
           descend = true;
         } else {
           res = combine(f, v3(0.0, 0.0, 0.0));
@@ -402,24 +400,25 @@ struct Tracer {
       if (sp == 0) { result = res; return true; }
       sp--;
       remaining++;
-      Frame& f = frames[sp];
-      if (f.state == 1) {
-        f.reflected = res * f.reflective;  // world.rs:113
-        if (f.need_refract) {
+      Frame& p = frames[sp];
+      if (p.state == 1) {
+        p.reflected = res * p.reflective;  // world.rs:113
+        if (p.need_refract) {
           rc.refract++;
-          f.state = 2;
-          ray = f.refr_ray;
+          p.state = 2;
+          child = p.refr_ray;
           descend = true;
         } else {
-          res = combine(f, v3(0.0, 0.0, 0.0));
+          res = combine(p, v3(0.0, 0.0, 0.0));
         }
       } else {
-        res = combine(f, res * f.transparency);  // world.rs:133
+        res = combine(p, res * p.transparency);  // world.rs:133
       }
     }
     sp++;
     remaining--;
-    qray = ray;
+    frames[sp].ray = child;
+    qray = child;
     q.init_closest(err);
     phase = PH_CLOSEST;
     return false;
@@ -431,7 +430,7 @@ RTC_HD V3 color_at(const SceneView& S, const RayD& ray, int max_depth, Scratch<H
                    uint32_t* err, double* t_out = nullptr) {
   Tracer tr;
   Frame frames[MAX_FRAMES];  // kept out of Tracer: a dynamically indexed member would pin the whole struct in local memory
-  tr.start(ray, max_depth, err);
+  tr.start(ray, max_depth, frames, err);
   for (;;) {
     search<HAS_CSG, FAITHFUL>(S, tr.qray, tr.q, scratch.csg(), &scratch.bvh, err);
     if (tr.advance(S, frames, scratch.neg, rc, err)) break;
@@ -484,18 +483,17 @@ RTC_HD void aa_offset(uint32_t aa, uint32_t s, double& ox, double& oy) {
 template <bool HAS_CSG, bool FAITHFUL>
 RTC_HD V3 render_pixel(const SceneView& S, const CameraD& cam, uint32_t px, uint32_t py, uint32_t aa, bool average,
                        int max_depth, Scratch<HAS_CSG>& scratch, RayCounters& rc, uint32_t* err) {
-  if (!average) {
+  // ONE color_at site for both (two would double the kernel's code and thrash the instruction cache)
+  V3 acc = v3(0.0, 0.0, 0.0);
+  const uint32_t n = average ? aa : 1u;
+  for (uint32_t s = 0; s < n; s++) {
+    double ox = 0.5, oy = 0.5;
+    if (average) aa_offset(aa, s, ox, oy);
     rc.primary++;
-    return color_at<HAS_CSG, FAITHFUL>(S, ray_for_pixel(cam, px, py, 0.5, 0.5), max_depth, scratch, rc, err);
+    V3 c = color_at<HAS_CSG, FAITHFUL>(S, ray_for_pixel(cam, px, py, ox, oy), max_depth, scratch, rc, err);
+    acc = average ? acc + c : c;
   }
-  V3 avg = v3(0.0, 0.0, 0.0);
-  for (uint32_t s = 0; s < aa; s++) {
-    double ox, oy;
-    aa_offset(aa, s, ox, oy);
-    rc.primary++;
-    avg = avg + color_at<HAS_CSG, FAITHFUL>(S, ray_for_pixel(cam, px, py, ox, oy), max_depth, scratch, rc, err);
-  }
-  return avg * (1.0 / (double)aa);
+  return average ? acc * (1.0 / (double)aa) : acc;
 }
 
 }  // namespace rtk
