@@ -30,13 +30,39 @@ struct BvhStack {
 // already validated for this ray (its ancestors are then valid too), -1 initially (= top level).
 // The slow part is rare (only for candidates the query wants) and kept out of line: it is six
 // IEEE divisions per box, and inlining it at every candidate site bloats the hot loop.
+// BoundingBox::intersects (bounding_box.rs:95-136) as a FILTERED predicate: the answer is only the
+// boolean tmin <= tmax, so first evaluate the slabs with one reciprocal per axis (6 multiplies
+// instead of 6 IEEE divisions); only if tmin and tmax are within 1e-9 (relative) of each other —
+// where the rounding of a/b versus a*(1/b) could flip the comparison — fall back to the reference's
+// own divisions. The EPSILON-parallel branch (num * INFINITY) involves no division and is taken
+// exactly as the reference takes it.
+RTC_HD bool ref_box_passes(const double* bx, const RayD& r, V3 inv) {
+  double tmin = -rt_inf(), tmax = rt_inf();
+  const double o[3] = {r.o.x, r.o.y, r.o.z}, d[3] = {r.d.x, r.d.y, r.d.z}, iv[3] = {inv.x, inv.y, inv.z};
+#if defined(__CUDACC__)
+#pragma unroll
+#endif
+  for (int a = 0; a < 3; a++) {
+    const double n0 = RTC_LDG(bx + a) - o[a], n1 = RTC_LDG(bx + 3 + a) - o[a];
+    const double m = fabs(d[a]) >= EPS ? iv[a] : rt_inf();
+    const double ta = n0 * m, tb = n1 * m;
+    tmin = fmax(tmin, ta > tb ? tb : ta);   // f64::max/min ignore NaN like fmax/fmin
+    tmax = fmin(tmax, ta > tb ? ta : tb);
+  }
+  const double slack = 1e-9 * (fabs(tmin) + fabs(tmax));
+  if (tmin <= tmax - slack) return true;    // ±inf and clear passes
+  if (tmin > tmax + slack) return false;    // clear misses
+  double e0, e1;                            // ambiguous (or NaN): the reference's exact arithmetic
+  return box_intersects(bx, r, e0, e1);
+}
+
 RTC_HD_NOINLINE bool chain_walk(const int32_t* parent, const rtc_node* nodes, const double* boxes, int32_t g, int32_t ok_group,
                                 RayD ray) {
+  const V3 inv = v3(1.0 / ray.d.x, 1.0 / ray.d.y, 1.0 / ray.d.z);
   while (g >= 0 && g != ok_group) {
-    double tmin, tmax;
     RTK_COUNT(chain_boxes, 1);
     int32_t bx = RTC_LDG(&nodes[g].aux);
-    if (!box_intersects(boxes + 6 * (size_t)bx, ray, tmin, tmax)) return false;
+    if (!ref_box_passes(boxes + 6 * (size_t)bx, ray, inv)) return false;
     g = RTC_LDG(parent + g);
   }
   return true;
@@ -51,10 +77,11 @@ RTC_HD bool chain_ok(const SceneView& S, int32_t g0, const RayD& ray, int32_t& o
 
 // Slab test against one of OUR boxes with the reciprocal direction. NaN (0*inf) drops out of
 // fmax/fmin, which is the conservative outcome; the boxes carry a guard band (build).
-RTC_HD bool own_box(const double* lo, const double* hi, const RayD& r, V3 inv, double& tmin, double& tmax) {
-  double ax = (RTC_LDG(lo + 0) - r.o.x) * inv.x, bx = (RTC_LDG(hi + 0) - r.o.x) * inv.x;
-  double ay = (RTC_LDG(lo + 1) - r.o.y) * inv.y, by = (RTC_LDG(hi + 1) - r.o.y) * inv.y;
-  double az = (RTC_LDG(lo + 2) - r.o.z) * inv.z, bz = (RTC_LDG(hi + 2) - r.o.z) * inv.z;
+RTC_HD bool own_box(double lx, double ly, double lz, double hx, double hy, double hz, const RayD& r, V3 inv, double& tmin,
+                    double& tmax) {
+  double ax = (lx - r.o.x) * inv.x, bx = (hx - r.o.x) * inv.x;
+  double ay = (ly - r.o.y) * inv.y, by = (hy - r.o.y) * inv.y;
+  double az = (lz - r.o.z) * inv.z, bz = (hz - r.o.z) * inv.z;
   tmin = fmax(fmax(fmin(ax, bx), fmin(ay, by)), fmin(az, bz));
   tmax = fmin(fmin(fmax(ax, bx), fmax(ay, by)), fmax(az, bz));
   // relative slack for the reciprocal's rounding
@@ -150,6 +177,7 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
         for (int32_t k = first; k < first + count && !C.done(); k++) {
           int32_t i, par;
           rtc_node nd;
+          LeafHits hits;
           RTK_COUNT(prim_tests, 1);
           if (k < S.n_always) {  // (uniform per run) every-ray prim: one 128-byte record
             const PrimRec* rec = S.recs + k;
@@ -169,23 +197,42 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
             }
             lr = ray_transform_v2(rec->inv, ray);
             lr_xf = -1;
-          } else {
-            i = RTC_LDG(S.prims + k);
-            nd = load_node(S.nodes + i);
-            par = -2;  // loaded on demand
-            if (nd.xform != lr_xf) {
-              lr = ray_transform(S.xforms + 12 * (size_t)nd.xform, ray);
-              lr_xf = nd.xform;
+            LeafHits h;
+            isect_leaf(S, nd, lr, h);
+            hits = h;
+          } else {  // BVH prim: one 96-byte record, geometry inline (no node → triangle indirection)
+            const LeafRec* lrec = S.leaf_recs + (k - S.n_always);
+#if defined(__CUDA_ARCH__)
+            const int4 hd = __ldg(reinterpret_cast<const int4*>(lrec));
+            i = hd.x; par = hd.z;
+            const int32_t xf = hd.y;
+            const uint32_t kf = (uint32_t)hd.w;
+#else
+            i = lrec->node; par = lrec->parent;
+            const int32_t xf = lrec->xform;
+            const uint32_t kf = lrec->kind_flags;
+#endif
+            nd.kind = (int32_t)(kf >> 24);
+            nd.flags = kf & 0xffffffu;
+            if (xf != lr_xf) {
+              lr = ray_transform(S.xforms + 12 * (size_t)xf, ray);
+              lr_xf = xf;
+            }
+            hits.n = 0;
+            hits.t0 = hits.t1 = hits.t2 = hits.t3 = 0.0;
+            if (nd.kind == RTC_SPHERE) {
+              isect_sphere(lr, [&](double t) { hits.push(t); });
+            } else {
+              double t, u, v;
+              if (isect_triangle(lr, lrec->g, t, u, v)) hits.push(t);
             }
           }
-          LeafHits h;
-          isect_leaf(S, nd, lr, h);
+          const LeafHits& h = hits;
 #if defined(__CUDACC__)
 #pragma unroll 1
 #endif
           for (int j = 0; j < h.n; j++) {
             const double t = j == 0 ? h.t0 : (j == 1 ? h.t1 : (j == 2 ? h.t2 : h.t3));
-            if (par == -2 && (t != t || C.want(t, i, nd.flags))) par = RTC_LDG(S.parent + i);
             cand(t, i, nd.flags, par);
           }
         }
@@ -200,14 +247,21 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
         const BvhNode* bn = S.bvh + cur;
         RTK_COUNT(bvh_nodes, 1);
 #if defined(__CUDA_ARCH__)
+        // the whole 128-byte node in seven 16-byte loads
+        const double2* bq = reinterpret_cast<const double2*>(bn);
+        const double2 q0 = __ldg(bq), q1 = __ldg(bq + 1), q2 = __ldg(bq + 2), q3 = __ldg(bq + 3), q4 = __ldg(bq + 4), q5 = __ldg(bq + 5);
         const int4 ci = __ldg(reinterpret_cast<const int4*>(&bn->c0));
         const int32_t c0 = ci.x, n0 = ci.y, c1 = ci.z, n1 = ci.w;
+        const double l0x = q0.x, l0y = q0.y, l0z = q1.x, h0x = q1.y, h0y = q2.x, h0z = q2.y;
+        const double l1x = q3.x, l1y = q3.y, l1z = q4.x, h1x = q4.y, h1y = q5.x, h1z = q5.y;
 #else
         const int32_t c0 = bn->c0, n0 = bn->n0, c1 = bn->c1, n1 = bn->n1;
+        const double l0x = bn->lo0[0], l0y = bn->lo0[1], l0z = bn->lo0[2], h0x = bn->hi0[0], h0y = bn->hi0[1], h0z = bn->hi0[2];
+        const double l1x = bn->lo1[0], l1y = bn->lo1[1], l1z = bn->lo1[2], h1x = bn->hi1[0], h1y = bn->hi1[1], h1z = bn->hi1[2];
 #endif
         double t0min = 0.0, t0max = 0.0, t1min = 0.0, t1max = 0.0;
-        const bool h0 = n0 >= 0 && own_box(bn->lo0, bn->hi0, ray, inv, t0min, t0max) && !C.cull(t0min, t0max);
-        const bool h1 = n1 >= 0 && own_box(bn->lo1, bn->hi1, ray, inv, t1min, t1max) && !C.cull(t1min, t1max);
+        const bool h0 = n0 >= 0 && own_box(l0x, l0y, l0z, h0x, h0y, h0z, ray, inv, t0min, t0max) && !C.cull(t0min, t0max);
+        const bool h1 = n1 >= 0 && own_box(l1x, l1y, l1z, h1x, h1y, h1z, ray, inv, t1min, t1max) && !C.cull(t1min, t1max);
         // refs: >= 0 inner node, < 0 leaf ~(first << 3 | count)
         const int32_t r0 = n0 > 0 ? ~((c0 << 3) | n0) : c0;
         const int32_t r1 = n1 > 0 ? ~((c1 << 3) | n1) : c1;

@@ -44,7 +44,17 @@ struct PrimRec {     // 128 bytes: everything the every-ray loop needs about one
   double inv[12];    // rows 0..2 of the leaf's transform_inverse (unused for a CSG prim)
 };
 
+struct LeafRec {     // 96 bytes: one BVH prim (triangle / smooth triangle / sphere), in BVH leaf order
+  int32_t node, xform, parent;
+  uint32_t kind_flags;   // kind << 24 | flags
+  double g[9];           // triangles: p1, e1, e2 (triangle.rs:14-21); spheres: unused
+  double _pad;
+};
+
+static_assert(sizeof(PrimRec) == 128 && sizeof(LeafRec) == 96 && sizeof(BvhNode) == 128, "record layout");
+
 struct AccelBuild {
+  std::vector<LeafRec> leaf_recs;  // one per BVH prim: prims[n_always + k] ↔ leaf_recs[k]
   std::vector<PrimRec> recs;       // one per always-prim, same order as prims[0, n_always)
   std::vector<int32_t> parent;     // per node: innermost enclosing Group node (outside CSGs), or -1
   std::vector<int32_t> prims;      // node indices: [0, n_always) tested for every ray (ascending), then BVH leaf order
@@ -147,7 +157,8 @@ constexpr int LEAF_MAX = 4;
 struct Builder {
   std::vector<Prim>& prims;
   AccelBuild& out;
-  explicit Builder(std::vector<Prim>& p, AccelBuild& o) : prims(p), out(o) {}
+  const rtc_scene_desc* desc;
+  explicit Builder(std::vector<Prim>& p, AccelBuild& o, const rtc_scene_desc* d) : prims(p), out(o), desc(d) {}
 
   // Split prims[b,e) — returns mid (b < mid < e), or -1 to make a leaf.
   int split(int b, int e, const Box& bounds, int depth) {
@@ -274,6 +285,16 @@ struct Builder {
       if (nd.n1 > 0) nd.c1 += shift;
     }
     for (int k = 0; k < n; k++) out.prims.push_back(prims[(size_t)k].node);
+    out.leaf_recs.assign((size_t)n, LeafRec{});
+    for (int k = 0; k < n; k++) {
+      const int32_t i = prims[(size_t)k].node;
+      const rtc_node& nd = desc->nodes[i];
+      LeafRec& r = out.leaf_recs[(size_t)k];
+      r.node = i; r.xform = nd.xform; r.parent = out.parent[(size_t)i];
+      r.kind_flags = ((uint32_t)nd.kind << 24) | (nd.flags & 0xffffffu);
+      if (nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE)
+        for (int c = 0; c < 9; c++) r.g[c] = desc->tri_p1e1e2[9 * (size_t)nd.aux + c];
+    }
   }
 };
 
@@ -310,6 +331,7 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
   A.prims.clear();
   A.n_always = 0;
   A.bvh.clear();
+  A.leaf_recs.clear();
   std::vector<Prim> cand;
   struct Open { int32_t end, node; };
   std::vector<Open> groups;
@@ -345,7 +367,7 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
   }
   A.n_always = (int32_t)A.prims.size();
   fill_recs(d, A);
-  Builder b(cand, A);
+  Builder b(cand, A, d);
   b.build();
 }
 

@@ -29,6 +29,7 @@ struct SceneView {
   const int32_t* prims;      // node indices: [0, n_always) tested for every ray, then BVH leaf order
   const BvhNode* bvh;        // binary BVH, node 0 = root
   const PrimRec* recs;       // one record per always-prim
+  const LeafRec* leaf_recs;  // one record per BVH prim (prims[n_always + k])
   int32_t n_nodes;
   int32_t n_lights;
   int32_t has_csg;

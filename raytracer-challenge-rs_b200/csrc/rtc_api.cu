@@ -212,9 +212,9 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   AccelBuild accel;
   build_accel(d, accel);
   // one slab: [nodes | xforms | boxes | limits | tri_geom | tri_normals | materials | patterns | lights | csg_parent
-  //            | parent | prims | bvh | recs]
+  //            | parent | prims | bvh | recs | leaf_recs]
   struct Part { const void* src; size_t bytes; size_t off; };
-  Part parts[14] = {
+  Part parts[15] = {
       {d->nodes, sizeof(rtc_node) * d->n_nodes, 0},
       {d->xforms, sizeof(double) * 12 * d->n_xforms, 0},
       {d->boxes, sizeof(double) * 6 * d->n_boxes, 0},
@@ -228,7 +228,8 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
       {accel.parent.data(), sizeof(int32_t) * accel.parent.size(), 0},
       {accel.prims.data(), sizeof(int32_t) * accel.prims.size(), 0},
       {accel.bvh.data(), sizeof(BvhNode) * accel.bvh.size(), 0},
-      {accel.recs.data(), sizeof(PrimRec) * accel.recs.size(), 0}};
+      {accel.recs.data(), sizeof(PrimRec) * accel.recs.size(), 0},
+      {accel.leaf_recs.data(), sizeof(LeafRec) * accel.leaf_recs.size(), 0}};
   size_t total = 0;
   for (auto& p : parts) {
     if (p.bytes && !p.src) return fail(RTC_ERR_INVALID, "a non-empty table has a NULL pointer");
@@ -273,6 +274,7 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   v.prims = (const int32_t*)(s->slab + parts[11].off);
   v.bvh = (const BvhNode*)(s->slab + parts[12].off);
   v.recs = (const PrimRec*)(s->slab + parts[13].off);
+  v.leaf_recs = (const LeafRec*)(s->slab + parts[14].off);
   v.n_always = accel.n_always;
   v.n_sph = accel.n_sph;
   v.n_pl = accel.n_pl;
