@@ -183,7 +183,10 @@ class FlatScene:
 
     def __del__(self):
         if getattr(self, "h", None):
-            host_lib().rth_flat_free(self.h)
+            try:
+                host_lib().rth_flat_free(self.h)
+            except TypeError:  # interpreter shutdown: module globals already cleared
+                pass
             self.h = None
 
 
@@ -199,7 +202,10 @@ class DeviceScene:
 
     def close(self):
         if getattr(self, "h", None):
-            cuda_lib().rtc_scene_destroy(self.h)
+            try:
+                cuda_lib().rtc_scene_destroy(self.h)
+            except TypeError:  # interpreter shutdown
+                pass
             self.h = None
 
     __del__ = close

@@ -95,7 +95,9 @@ EMUL_API int emul_render(const rtc_scene_desc* d, const rtc_camera* c, const rtc
   for (unsigned t = 0; t < threads; t++) {
     th.emplace_back([&, t]() {
       // interleaved rows for load balance
+      const uint32_t nranks = o->nranks ? o->nranks : 1, tile_rows = o->tile_rows ? o->tile_rows : 8;
       for (uint32_t y = y0 + t; y < y1; y += threads) {
+        if ((y / tile_rows) % nranks != o->rank) continue;  // rtc_opts sharding: tile t belongs to rank t % nranks
         if (b.view.has_csg) { if (fa) rows<true, true>(b.view, cam, y, y + 1, o->aa_samples, avg, (int)o->max_depth, rgb, per[t].data());
                               else rows<true, false>(b.view, cam, y, y + 1, o->aa_samples, avg, (int)o->max_depth, rgb, per[t].data()); }
         else { if (fa) rows<false, true>(b.view, cam, y, y + 1, o->aa_samples, avg, (int)o->max_depth, rgb, per[t].data());
