@@ -17,6 +17,7 @@ struct RenderParams {
   uint32_t row_begin, row_end;  // frame rows rendered by this call
   uint32_t tile_rows, rank, nranks;
   uint32_t owned_rows;          // rows of the launch domain (owned tiles * tile_rows)
+  uint32_t oy0;                 // first owned row of THIS launch (row bands: render band k+1 while band k is copied out)
   uint32_t aa, average;
   int32_t max_depth;
   uint32_t faithful;             // RTC_OPT_FAITHFUL_TRAVERSAL: the reference's own search order
@@ -54,7 +55,7 @@ __global__ void __launch_bounds__(128, RTK_MIN_BLOCKS) render_kernel(SceneView S
                                                                      unsigned long long* __restrict__ counters) {
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   const uint32_t px = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
-  const uint32_t oy = blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
+  const uint32_t oy = P.oy0 + blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
   if (px >= cam.hsize || oy >= P.owned_rows) return;
   // owned row index → frame row: tile (rank + k*nranks), row within tile
   const uint32_t k = oy / P.tile_rows, r = oy - k * P.tile_rows;

@@ -5,6 +5,7 @@
 #include <chrono>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -166,13 +167,16 @@ int make_params(const rtc_camera* c, const rtc_opts* o, RenderParams& P, bool& f
   return RTC_OK;
 }
 
-int launch_frame(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool faithful, double* out, cudaStream_t stream) {
-  CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, N_COUNTERS * sizeof(unsigned long long), stream));
-  dim3 block(128), grid((cam.hsize + 15) / 16, (P.owned_rows + 7) / 8);
-  CUDA_TRY(cudaEventRecord(s->ev0, stream));
+// One launch over owned rows [oy0, oy0 + rows) of the launch domain (rows == 0: the whole domain).
+int launch_rows(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool faithful, double* out, cudaStream_t stream,
+                uint32_t oy0, uint32_t rows) {
+  RenderParams Pk = P;
+  Pk.faithful = faithful ? 1u : 0u;
+  Pk.oy0 = oy0;
+  if (rows == 0) rows = P.owned_rows > oy0 ? P.owned_rows - oy0 : 0;
+  if (oy0 + rows < Pk.owned_rows) Pk.owned_rows = oy0 + rows;
+  dim3 block(128), grid((cam.hsize + 15) / 16, (rows + 7) / 8);
   if (grid.x > 0 && grid.y > 0) {
-    RenderParams Pk = P;
-    Pk.faithful = faithful ? 1u : 0u;
     if (s->has_csg) {
       if (faithful) render_kernel<true, true><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
       else render_kernel<true, false><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
@@ -182,10 +186,47 @@ int launch_frame(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool f
     }
     s->launches++;
   }
-  CUDA_TRY(cudaEventRecord(s->ev1, stream));
   CUDA_TRY(cudaGetLastError());
   return RTC_OK;
 }
+
+int launch_frame(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool faithful, double* out, cudaStream_t stream) {
+  CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, N_COUNTERS * sizeof(unsigned long long), stream));
+  CUDA_TRY(cudaEventRecord(s->ev0, stream));
+  int rc = launch_rows(s, cam, P, faithful, out, stream, 0, 0);
+  if (rc) return rc;
+  CUDA_TRY(cudaEventRecord(s->ev1, stream));
+  return RTC_OK;
+}
+
+// Device canvases are expensive to allocate (49.8 MB at 1080p): keep one freed canvas per device.
+struct CanvasPool {
+  std::mutex mu;
+  double* ptr[16] = {nullptr};
+  size_t doubles[16] = {0};
+  double* take(int dev, size_t need, size_t& got) {
+    std::lock_guard<std::mutex> g(mu);
+    if (dev >= 0 && dev < 16 && ptr[dev] && doubles[dev] >= need) {
+      double* p = ptr[dev];
+      got = doubles[dev];
+      ptr[dev] = nullptr;
+      doubles[dev] = 0;
+      return p;
+    }
+    return nullptr;
+  }
+  void give(int dev, double* p, size_t n) {
+    {
+      std::lock_guard<std::mutex> g(mu);
+      if (dev >= 0 && dev < 16 && doubles[dev] < n) {
+        std::swap(ptr[dev], p);
+        std::swap(doubles[dev], n);
+      }
+    }
+    if (p) cudaFree(p);
+  }
+};
+CanvasPool g_canvas_pool;
 
 }  // namespace
 
@@ -247,12 +288,29 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
     return fail(RTC_ERR_CUDA, m);
   };
   cudaError_t e;
-  if ((e = cudaMalloc((void**)&s->slab, total)) != cudaSuccess) return bail(e, "cudaMalloc(scene)");
+  // Stream-ordered allocation from the device's default pool (kept warm: release threshold = max),
+  // so creating and destroying a scene per frame costs no cudaMalloc/cudaFree round trip.
+  {
+    static std::mutex mu;
+    static bool pool_ready[64] = {false};
+    std::lock_guard<std::mutex> g(mu);
+    if (device < 64 && !pool_ready[device]) {
+      cudaMemPool_t pool;
+      if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+        unsigned long long thr = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+      }
+      cudaGetLastError();
+      pool_ready[device] = true;
+    }
+  }
   if ((e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+  const size_t tail = align_up(N_COUNTERS * sizeof(unsigned long long)) + align_up(32 * sizeof(double));
+  if ((e = cudaMallocAsync((void**)&s->slab, total + tail, s->stream)) != cudaSuccess) return bail(e, "cudaMallocAsync(scene)");
+  s->d_counters = (unsigned long long*)(s->slab + total);
+  s->d_probe = (double*)(s->slab + total + align_up(N_COUNTERS * sizeof(unsigned long long)));
   if ((e = cudaEventCreate(&s->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
   if ((e = cudaEventCreate(&s->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
-  if ((e = cudaMalloc((void**)&s->d_counters, N_COUNTERS * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "cudaMalloc(counters)");
-  if ((e = cudaMalloc((void**)&s->d_probe, 32 * sizeof(double))) != cudaSuccess) return bail(e, "cudaMalloc(probe)");
   // stage on the host, one H2D copy
   std::vector<char> stage(total, 0);
   for (auto& p : parts)
@@ -289,10 +347,11 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
 void rtc_scene_destroy(rtc_scene* s) {
   if (!s) return;
   cudaSetDevice(s->device);
-  if (s->slab) cudaFree(s->slab);
-  if (s->d_counters) cudaFree(s->d_counters);
-  if (s->d_canvas) cudaFree(s->d_canvas);
-  if (s->d_probe) cudaFree(s->d_probe);
+  if (s->slab) {
+    if (s->stream) cudaFreeAsync(s->slab, s->stream); else cudaFree(s->slab);
+  }
+  if (s->d_canvas) g_canvas_pool.give(s->device, s->d_canvas, s->canvas_doubles);
+
   if (s->ev0) cudaEventDestroy(s->ev0);
   if (s->ev1) cudaEventDestroy(s->ev1);
   if (s->stream) cudaStreamDestroy(s->stream);
@@ -349,22 +408,48 @@ int rtc_render(rtc_scene* s, const rtc_camera* camera, const rtc_opts* opts, dou
   if (rc) return rc;
   CUDA_TRY(cudaSetDevice(s->device));
   size_t need = (size_t)cam.hsize * cam.vsize * 3;
+  {
+    // Zero-copy canvas: if the caller's canvas is pinned, mapped host memory (cudaHostAlloc /
+    // cudaHostRegister — what a pinned torch tensor is), the kernel stores its pixels straight into
+    // it over PCIe (24 B per pixel, posted writes spread over the whole kernel) and there is no
+    // device canvas and no device→host copy at all.
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, rgb_host) == cudaSuccess && attr.type == cudaMemoryTypeHost && attr.devicePointer) {
+      s->launches = 0;
+      rc = launch_frame(s, cam, P, faithful, (double*)attr.devicePointer, s->stream);
+      if (rc) return rc;
+      rtc_stats local;
+      rc = rtc_scene_finish(s, s->stream, &local);
+      local.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+      if (stats) *stats = local;
+      return rc;
+    }
+    cudaGetLastError();  // pageable memory: not an error, take the staged path
+  }
   if (s->canvas_doubles < need) {
-    if (s->d_canvas) cudaFree(s->d_canvas);
+    if (s->d_canvas) g_canvas_pool.give(s->device, s->d_canvas, s->canvas_doubles);
     s->d_canvas = nullptr;
     s->canvas_doubles = 0;
-    CUDA_TRY(cudaMalloc((void**)&s->d_canvas, need * sizeof(double)));
-    s->canvas_doubles = need;
+    size_t got = 0;
+    s->d_canvas = g_canvas_pool.take(s->device, need, got);
+    if (s->d_canvas) {
+      s->canvas_doubles = got;
+    } else {
+      CUDA_TRY(cudaMalloc((void**)&s->d_canvas, need * sizeof(double)));
+      s->canvas_doubles = need;
+    }
   }
   s->launches = 0;
-  rc = launch_frame(s, cam, P, faithful, s->d_canvas, s->stream);
-  if (rc) return rc;
-  // device → host: only the rows this call rendered (owned tiles clipped to the row range)
   const size_t row_doubles = (size_t)cam.hsize * 3;
   if (P.nranks <= 1) {
+    rc = launch_frame(s, cam, P, faithful, s->d_canvas, s->stream);
+    if (rc) return rc;
     size_t off = (size_t)P.row_begin * row_doubles, cnt = (size_t)(P.row_end - P.row_begin) * row_doubles;
     if (cnt) CUDA_TRY(cudaMemcpyAsync(rgb_host + off, s->d_canvas + off, cnt * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
   } else {
+    rc = launch_frame(s, cam, P, faithful, s->d_canvas, s->stream);
+    if (rc) return rc;
+    // device → host: only the rows this call rendered (owned tiles clipped to the row range)
     for (uint32_t t = P.rank; (size_t)t * P.tile_rows < cam.vsize; t += P.nranks) {
       uint32_t y0 = t * P.tile_rows, y1 = y0 + P.tile_rows;
       if (y0 < P.row_begin) y0 = P.row_begin;

@@ -147,3 +147,24 @@ def test_device_quantize_kernel(pkg):
     torch.cuda.synchronize()
     assert np.array_equal(y.cpu().numpy(), pkg.quantize(vals))
     assert list(y.cpu().numpy()[:5]) == [0, 0, 128, 255, 255]   # ppm.rs:105-124
+
+
+def test_pinned_canvas_is_written_zero_copy(pkg, prod):
+    """rtc_render into a PINNED host canvas: the kernel stores its pixels straight into it over PCIe
+    (no device canvas, no D2H copy) — must equal the staged path (pageable canvas) bit for bit."""
+    import torch
+    w, c = scenes.reflect_refract(prod, 320, 180)
+    ds = pkg.DeviceScene(pkg.FlatScene(w))
+    staged, st0 = ds.render(c)
+    pinned = torch.full((180, 320, 3), -7.0, dtype=torch.float64).pin_memory()
+    cam, opts, st = pkg.camera_to_rtc(c), pkg.make_opts(), pkg.RtcStats()
+    pkg._check(pkg.cuda_lib().rtc_render(ds.h, C.byref(cam), C.byref(opts), pinned.data_ptr(), C.byref(st)))
+    assert np.array_equal(pinned.numpy(), staged)
+    assert st.rays == st0.rays
+    # row range: only rows [40,100) are written
+    pinned.fill_(-7.0)
+    opts = pkg.make_opts(rows=(40, 100))
+    pkg._check(pkg.cuda_lib().rtc_render(ds.h, C.byref(cam), C.byref(opts), pinned.data_ptr(), C.byref(st)))
+    got = pinned.numpy()
+    assert np.array_equal(got[40:100], staged[40:100]) and np.all(got[:40] == -7.0) and np.all(got[100:] == -7.0)
+    ds.close()
