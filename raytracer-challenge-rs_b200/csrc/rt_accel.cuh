@@ -59,7 +59,11 @@ RTC_HD bool ref_box_passes(const double* bx, const RayD& r, V3 inv) {
 RTC_HD_NOINLINE bool chain_walk(const int32_t* parent, const rtc_node* nodes, const double* boxes, int32_t g, int32_t ok_group,
                                 RayD ray) {
   const V3 inv = v3(1.0 / ray.d.x, 1.0 / ray.d.y, 1.0 / ray.d.z);
-  while (g >= 0 && g != ok_group) {
+  while (g >= 0) {
+    // already validated? ok_group and all its ancestors are; in pre-order, g is an ancestor-or-self
+    // of ok_group iff g <= ok_group < skip(g) — so a sibling subtree costs one box, not the whole chain
+    const int32_t skip = RTC_LDG(&nodes[g].skip);
+    if (g <= ok_group && ok_group < skip) break;
     RTK_COUNT(chain_boxes, 1);
     int32_t bx = RTC_LDG(&nodes[g].aux);
     if (!ref_box_passes(boxes + 6 * (size_t)bx, ray, inv)) return false;
@@ -77,13 +81,24 @@ RTC_HD bool chain_ok(const SceneView& S, int32_t g0, const RayD& ray, int32_t& o
 
 // Slab test against one of OUR boxes with the reciprocal direction. NaN (0*inf) drops out of
 // fmax/fmin, which is the conservative outcome; the boxes carry a guard band (build).
-RTC_HD bool own_box(double lx, double ly, double lz, double hx, double hy, double hz, const RayD& r, V3 inv, double& tmin,
-                    double& tmax) {
+// `plain`: no direction component is zero, so no 0*inf NaN can arise and min/max are single
+// compare+select pairs instead of the NaN-aware fmin/fmax sequences.
+RTC_HD bool own_box(double lx, double ly, double lz, double hx, double hy, double hz, const RayD& r, V3 inv, bool plain,
+                    double& tmin, double& tmax) {
   double ax = (lx - r.o.x) * inv.x, bx = (hx - r.o.x) * inv.x;
   double ay = (ly - r.o.y) * inv.y, by = (hy - r.o.y) * inv.y;
   double az = (lz - r.o.z) * inv.z, bz = (hz - r.o.z) * inv.z;
-  tmin = fmax(fmax(fmin(ax, bx), fmin(ay, by)), fmin(az, bz));
-  tmax = fmin(fmin(fmax(ax, bx), fmax(ay, by)), fmax(az, bz));
+  if (plain) {
+    const double x0 = ax < bx ? ax : bx, x1 = ax < bx ? bx : ax;
+    const double y0 = ay < by ? ay : by, y1 = ay < by ? by : ay;
+    const double z0 = az < bz ? az : bz, z1 = az < bz ? bz : az;
+    const double m0 = x0 > y0 ? x0 : y0, m1 = x1 < y1 ? x1 : y1;
+    tmin = m0 > z0 ? m0 : z0;
+    tmax = m1 < z1 ? m1 : z1;
+  } else {
+    tmin = fmax(fmax(fmin(ax, bx), fmin(ay, by)), fmin(az, bz));
+    tmax = fmin(fmin(fmax(ax, bx), fmax(ay, by)), fmax(az, bz));
+  }
   // relative slack for the reciprocal's rounding
   return tmin <= tmax + 1e-9 * (fabs(tmin) + fabs(tmax));
 }
@@ -115,7 +130,7 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
     RayD lr;
     int32_t lr_xf = -1;
     V3 inv = v3(0.0, 0.0, 0.0);
-    bool have_inv = false;
+    bool have_inv = false, plain = false;
     int sp = 0;
     // one candidate intersection: want → validate against the reference's group chain → take
     auto cand = [&](double t, int32_t i, uint32_t flags, int32_t par) {
@@ -239,6 +254,7 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
         if (C.done() || S.n_bvh <= 0) return;
         if (!have_inv) {  // the always-run is done: enter the BVH at its root
           inv = v3(1.0 / ray.d.x, 1.0 / ray.d.y, 1.0 / ray.d.z);
+          plain = ray.d.x != 0.0 && ray.d.y != 0.0 && ray.d.z != 0.0 && ray.d.x == ray.d.x && ray.d.y == ray.d.y && ray.d.z == ray.d.z;
           have_inv = true;
           cur = 0;
           continue;
@@ -260,8 +276,8 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
         const double l1x = bn->lo1[0], l1y = bn->lo1[1], l1z = bn->lo1[2], h1x = bn->hi1[0], h1y = bn->hi1[1], h1z = bn->hi1[2];
 #endif
         double t0min = 0.0, t0max = 0.0, t1min = 0.0, t1max = 0.0;
-        const bool h0 = n0 >= 0 && own_box(l0x, l0y, l0z, h0x, h0y, h0z, ray, inv, t0min, t0max) && !C.cull(t0min, t0max);
-        const bool h1 = n1 >= 0 && own_box(l1x, l1y, l1z, h1x, h1y, h1z, ray, inv, t1min, t1max) && !C.cull(t1min, t1max);
+        const bool h0 = n0 >= 0 && own_box(l0x, l0y, l0z, h0x, h0y, h0z, ray, inv, plain, t0min, t0max) && !C.cull(t0min, t0max);
+        const bool h1 = n1 >= 0 && own_box(l1x, l1y, l1z, h1x, h1y, h1z, ray, inv, plain, t1min, t1max) && !C.cull(t1min, t1max);
         // refs: >= 0 inner node, < 0 leaf ~(first << 3 | count)
         const int32_t r0 = n0 > 0 ? ~((c0 << 3) | n0) : c0;
         const int32_t r1 = n1 > 0 ? ~((c1 << 3) | n1) : c1;

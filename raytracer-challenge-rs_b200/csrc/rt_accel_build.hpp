@@ -358,6 +358,30 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
       i = i + 1;
     }
   }
+  // Nested boxes let one test stand for a whole chain. For one ray, per-axis slab intervals are
+  // monotone in the box bounds even in floating point (x - o and x / d are monotone, and the
+  // EPSILON-parallel branch only asks "inside the slab?"), so if box(g) ⊆ box(a) component-wise
+  // (all finite) then passing g's box implies passing a's. parent[g] of a GROUP therefore skips
+  // every ancestor that contains g's box and names the first one that does not (normally none:
+  // Group boxes are unions of their children's, group.rs:128-133). Leaves keep their innermost group.
+  {
+    auto contains = [&](int32_t a, int32_t c) {
+      const double* A_ = d->boxes + 6 * (size_t)d->nodes[a].aux;
+      const double* C_ = d->boxes + 6 * (size_t)d->nodes[c].aux;
+      for (int k = 0; k < 6; k++)
+        if (!std::isfinite(A_[k]) || !std::isfinite(C_[k])) return false;
+      for (int k = 0; k < 3; k++)
+        if (!(A_[k] <= C_[k] && C_[k + 3] <= A_[k + 3] && C_[k] <= C_[k + 3])) return false;
+      return true;
+    };
+    std::vector<int32_t> real_parent = A.parent;
+    for (int32_t g = 0; g < n; g++) {
+      if (d->nodes[g].kind != RTC_GROUP) continue;
+      int32_t a = real_parent[(size_t)g];
+      while (a >= 0 && contains(a, g)) a = real_parent[(size_t)a];
+      A.parent[(size_t)g] = a;
+    }
+  }
   if ((int)cand.size() < BVH_MIN_PRIMS) {
     for (auto& p : cand) A.prims.push_back(p.node);
     std::sort(A.prims.begin(), A.prims.end());
