@@ -11,7 +11,8 @@ counted on the device), ms_per_step = frame ms.
   value   scene resident in HBM, K frames timed with CUDA events on the launching stream (max over
           ranks), L2 flushed between frames.
   e2e     the reference-facing call with HOST buffers: flatten(World) → H2D scene upload → render →
-          D2H canvas into pinned host memory, every step (public API: DeviceScene / rtc_render).
+          canvas in pinned host memory, every step (public API: DeviceScene / rtc_render; the kernel
+          stores its pixels straight into the pinned canvas over PCIe — that IS the D2H transfer).
   N > 1   one process per GPU (torchrun); the frame's row tiles are sharded cyclically and each
           rank's kernel stores its pixels directly into rank 0's canvas over NVLink (CUDA IPC
           peer mapping); falls back to one NCCL reduce if peer mapping is unavailable. scaling = strong.
@@ -120,7 +121,7 @@ def run_reference(args, pkg, scenes):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--workload", default="reflect_refract_1080p")
@@ -301,16 +302,23 @@ def main():
             cpu_baseline["parity_identical_8bit"] = float(np.mean(np.all(q(got) == q(want), axis=-1)))
             cpu_baseline["parity_max_linear_diff"] = float(np.max(np.abs(got - want)))
             cpu_baseline["rays_match"] = bool(budget_rows < H or info["rays"] == rays_frame)
+        # dram bytes per launch of the render kernel from the committed ncu --set full capture, if any
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+                traffic = json.load(fh).get(args.workload, {}).get("dram_bytes_per_launch")
+        except Exception:
+            traffic = None
         if flops_frame is not None:
             achieved = flops_frame / (ms_per_step * 1e-3) / 1e12
             roofline = {"bound": "fp64", "achieved": achieved, "peak": peak_nofma / 1e3, "unit": "TFLOP/s",
-                        "frac": achieved / (peak_nofma / 1e3), "traffic": None,
+                        "frac": achieved / (peak_nofma / 1e3), "traffic": traffic,
                         "peak_source": "measured in this run: rtc_measure_fp64 (DMUL+DADD stream, non-fused — the library is built --fmad=false); MEASURED_PEAKS.json has no FP64 figure",
                         "peak_dfma_tflops": peak_fma / 1e3, "frac_of_dfma_peak": achieved / (peak_fma / 1e3),
                         "algorithmic_flops_per_frame": flops_frame,
                         "flop_definition": "one per + - * / sqrt as written in the reference (SURVEY 8-a constants), counted by the oracle"}
         else:
-            roofline = {"bound": "fp64", "achieved": None, "peak": peak_nofma / 1e3, "unit": "TFLOP/s", "frac": None, "traffic": None,
+            roofline = {"bound": "fp64", "achieved": None, "peak": peak_nofma / 1e3, "unit": "TFLOP/s", "frac": None, "traffic": traffic,
                         "peak_dfma_tflops": peak_fma / 1e3}
 
     if rank == 0:
