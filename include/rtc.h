@@ -186,6 +186,13 @@ RTC_API int rtc_scene_finish(rtc_scene* scene, void* stream, rtc_stats* stats);
  * NaN→0, for n doubles already on the device → n bytes on the device. */
 RTC_API int rtc_quantize_device(int device, const double* rgb_dev, size_t n, uint8_t* rgb8_dev, void* stream);
 
+/* Camera::render for a caller that wants an image file (scene-parser/src/lib.rs:278-281 →
+ * image/png.rs:13-31, image/ppm.rs:24-75): render into a device canvas, quantise there, and copy
+ * 3 bytes per pixel to `rgb8_host` (hsize*vsize*3 bytes, rows row_begin..row_end written) instead of
+ * 24. nranks must be 1. */
+RTC_API int rtc_render_rgb8(rtc_scene* scene, const rtc_camera* camera, const rtc_opts* opts, uint8_t* rgb8_host,
+                    rtc_stats* stats);
+
 /* Debug / known-answer entry: World::color_at(ray, remaining) (world.rs:70) for a batch of HOST
  * rays. rgb_out (3n) and t_out (n; hit t or -1) may each be NULL. */
 RTC_API int rtc_trace_rays(rtc_scene* scene, size_t n, const double* origins, const double* directions,

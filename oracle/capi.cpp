@@ -27,7 +27,7 @@ extern "C" {
 struct orc_material {
   double color[3];
   double ambient, diffuse, specular, shininess, reflective, transparency, refractive_index;
-  int32_t has_pattern;
+  int32_t has_pattern;   // bit 0: material has a pattern; bit 1: the pattern had set_transform called
   int32_t pattern_kind;  // 0 test, 1 stripe, 2 gradient, 3 ring, 4 checkers
   double pattern_a[3], pattern_b[3];
   double pattern_transform[16];
@@ -103,7 +103,7 @@ int orc_shape_set_material(void* s, const orc_material* m) {
     if (m->has_pattern) {
       Pattern p = make_pattern((PatternKind)m->pattern_kind, Color(m->pattern_a[0], m->pattern_a[1], m->pattern_a[2]),
                                Color(m->pattern_b[0], m->pattern_b[1], m->pattern_b[2]));
-      p.set_transform(mat16(m->pattern_transform));
+      if (m->has_pattern & 2) p.set_transform(mat16(m->pattern_transform));  // bit 1: set_transform was called
       mat.set_pattern(p);
     }
     ((Shape*)s)->set_material(mat);

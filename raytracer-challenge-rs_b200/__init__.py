@@ -93,6 +93,7 @@ def cuda_lib():
         lib.rtc_render_device.argtypes = [vp, C.POINTER(RtcCamera), C.POINTER(RtcOpts), pd, vp, C.POINTER(RtcStats)]
         lib.rtc_scene_finish.argtypes = [vp, vp, C.POINTER(RtcStats)]
         lib.rtc_quantize_device.argtypes = [C.c_int, pd, sz, pd, vp]
+        lib.rtc_render_rgb8.argtypes = [vp, C.POINTER(RtcCamera), C.POINTER(RtcOpts), pd, C.POINTER(RtcStats)]
         lib.rtc_trace_rays.argtypes = [vp, sz, pd, pd, u32, pd, pd]
         lib.rtc_probe_hit.argtypes = [vp, pd, pd, pd]
         lib.rtc_is_shadowed.argtypes = [vp, pd, u32]
@@ -133,6 +134,9 @@ def host_lib():
         lib.rth_canvas_to_ppm.argtypes = [vp, C.c_size_t, C.c_size_t, vp, C.c_size_t]
         lib.rth_canvas_to_ppm.restype = C.c_size_t
         lib.rth_save_ppm.argtypes = [vp, C.c_size_t, C.c_size_t, C.c_char_p]
+        lib.rth_save_p6.argtypes = [vp, C.c_size_t, C.c_size_t, C.c_char_p]
+        lib.rth_save_png.argtypes = [vp, C.c_size_t, C.c_size_t, C.c_char_p]
+        lib.rth_render_scene_file.argtypes = [C.c_char_p, C.c_char_p, C.c_uint32, C.c_uint32, C.c_int, C.POINTER(RtcStats)]
         _libs["host"] = lib
     return _libs["host"]
 
@@ -210,6 +214,12 @@ class DeviceScene:
 
     __del__ = close
 
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
     def render(self, camera, out=None, **opts):
         """rtc_render into a host canvas (numpy float64 [vsize, hsize, 3]); returns (canvas, stats)."""
         cam = camera_to_rtc(camera)
@@ -218,6 +228,16 @@ class DeviceScene:
         o = make_opts(**opts)
         st = RtcStats()
         _check(cuda_lib().rtc_render(self.h, C.byref(cam), C.byref(o), out.ctypes.data, C.byref(st)))
+        return out, st
+
+    def render_rgb8(self, camera, out=None, **opts):
+        """rtc_render_rgb8: the frame as 8-bit pixels (uint8 [vsize, hsize, 3]), quantised on the device."""
+        cam = camera_to_rtc(camera)
+        if out is None:
+            out = np.zeros((cam.vsize, cam.hsize, 3), dtype=np.uint8)
+        o = make_opts(**opts)
+        st = RtcStats()
+        _check(cuda_lib().rtc_render_rgb8(self.h, C.byref(cam), C.byref(o), out.ctypes.data, C.byref(st)))
         return out, st
 
     def render_device(self, camera, dev_ptr, stream=None, stats=False, **opts):
@@ -291,6 +311,24 @@ def canvas_to_ppm(canvas):
     buf = C.create_string_buffer(n)
     host_lib().rth_canvas_to_ppm(c.ctypes.data, w, h, buf, n)
     return buf.raw
+
+
+def save_image(rgb8, path):
+    """Write 8-bit pixels (uint8 [h, w, 3]) as .png (image/png.rs:13-31) or binary P6."""
+    img = np.ascontiguousarray(rgb8, dtype=np.uint8)
+    fn = host_lib().rth_save_png if str(path).endswith(".png") else host_lib().rth_save_p6
+    if fn(img.ctypes.data, img.shape[1], img.shape[0], os.fsencode(str(path))) != 0:
+        raise OSError(scene_api().last_error())
+
+
+def render_scene_file(scene_path, out_path, extended=False, aa=1, device=0):
+    """scene-parser's `render_scene <scene-file> <output-file>` on the CUDA backend; returns RtcStats."""
+    st = RtcStats()
+    rc = host_lib().rth_render_scene_file(os.fsencode(str(scene_path)), os.fsencode(str(out_path)),
+                                          1 if extended else 0, aa, device, C.byref(st))
+    if rc != 0:
+        raise RtcError(rc, scene_api().last_error()) if rc < 0 else OSError(scene_api().last_error())
+    return st
 
 
 def measure_fp64(device=0, fused=False):

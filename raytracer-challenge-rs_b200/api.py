@@ -9,6 +9,7 @@ The objects mirror the reference's API names: World / Camera / shapes / Material
 (raytracer/src/{world,camera,material}.rs, geometry/shape/*.rs, pattern/mod.rs).
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -33,7 +34,9 @@ class Pattern:
 
     def __init__(self, kind=PAT_TEST, a=(0.0, 0.0, 0.0), b=(0.0, 0.0, 0.0), transform=None):
         self.kind, self.a, self.b = kind, tuple(map(float, a)), tuple(map(float, b))
-        self.transform = list(transform) if transform is not None else list(_IDENTITY)
+        # None = set_transform never called: the reference keeps the exact identity then, while
+        # set_transform(identity) stores identity.inverse() with its negative zeros (pattern/mod.rs:22-36)
+        self.transform = list(transform) if transform is not None else None
 
     def set_transform(self, m):
         self.transform = list(m)
@@ -84,12 +87,12 @@ class Material:
         c.color[:] = self.color
         c.ambient, c.diffuse, c.specular, c.shininess = self.ambient, self.diffuse, self.specular, self.shininess
         c.reflective, c.transparency, c.refractive_index = self.reflective, self.transparency, self.refractive_index
-        c.has_pattern = 1 if self.pattern is not None else 0
         p = self.pattern or Pattern()
+        c.has_pattern = (1 if self.pattern is not None else 0) | (2 if p.transform is not None else 0)
         c.pattern_kind = p.kind
         c.pattern_a[:] = p.a
         c.pattern_b[:] = p.b
-        c.pattern_transform[:] = p.transform
+        c.pattern_transform[:] = p.transform if p.transform is not None else _IDENTITY
         return c
 
 
@@ -174,9 +177,9 @@ class Shape:
 class World:
     """world.rs:18-29,83-93"""
 
-    def __init__(self, api):
+    def __init__(self, api, handle=None):
         self.api = api
-        self.h = api._f("world_new")()
+        self.h = handle if handle else api._f("world_new")()
         self.n_lights = 0
 
     def __del__(self):
@@ -197,9 +200,9 @@ class World:
 class Camera:
     """camera.rs:20-55,128-131"""
 
-    def __init__(self, api, hsize, vsize, field_of_view):
+    def __init__(self, api, hsize, vsize, field_of_view, handle=None):
         self.api, self.hsize, self.vsize, self.field_of_view = api, int(hsize), int(vsize), float(field_of_view)
-        self.h = api._f("camera_new")(self.hsize, self.vsize, self.field_of_view)
+        self.h = handle if handle else api._f("camera_new")(self.hsize, self.vsize, self.field_of_view)
         self.aa_samples = 1
 
     def __del__(self):
@@ -254,6 +257,16 @@ class SceneApi:
             "camera_set_transform": (i32, [vp, pd]),
             "camera_params": (None, [vp, pd]),
         }
+        # front ends only the host library has (the oracle is handed their output)
+        optional = {
+            "yaml_load": (i32, [C.c_char_p, sz, C.c_uint32, C.c_char_p, C.POINTER(vp), C.POINTER(vp), C.POINTER(i32)]),
+            "camera_dims": (None, [vp, C.POINTER(sz), C.POINTER(sz), C.POINTER(d)]),
+            "world_counts": (None, [vp, C.POINTER(sz), C.POINTER(sz)]),
+            "world_object": (vp, [vp, sz]),
+        }
+        for name, sig in optional.items():
+            if hasattr(lib, prefix + name):
+                sigs[name] = sig
         for name, (res, args) in sigs.items():
             fn = getattr(lib, prefix + name)
             fn.restype, fn.argtypes = res, args
@@ -310,6 +323,24 @@ class SceneApi:
         if not h:
             raise ValueError(self.last_error())
         return Shape(self, h)
+
+    def yaml_scene(self, text, extended=False, base_dir=None):
+        """scene-parser SceneParser::load_file (lib.rs:90-119) → (World, Camera | None, skipped `add` kinds)"""
+        data = text.encode() if isinstance(text, str) else text
+        w, c, skipped = C.c_void_p(), C.c_void_p(), C.c_int(0)
+        bd = os.fsencode(base_dir) if base_dir else None
+        if self._f("yaml_load")(data, len(data), 1 if extended else 0, bd, C.byref(w), C.byref(c), C.byref(skipped)) != 0:
+            raise ValueError(self.last_error())
+        world = World(self, handle=w.value)
+        no, nl = C.c_size_t(), C.c_size_t()
+        self._f("world_counts")(world.h, C.byref(no), C.byref(nl))
+        world.n_objects, world.n_lights = no.value, nl.value
+        camera = None
+        if c.value:
+            hs, vs, fov = C.c_size_t(), C.c_size_t(), C.c_double()
+            self._f("camera_dims")(c.value, C.byref(hs), C.byref(vs), C.byref(fov))
+            camera = Camera(self, hs.value, vs.value, fov.value, handle=c.value)
+        return world, camera, skipped.value
 
     def world(self):
         return World(self)

@@ -60,6 +60,12 @@ def build_host(force=False):
     if force or _newer(out, srcs + [cuda]):
         _run(["g++"] + GXX_FLAGS + ["-shared", "-o", out, os.path.join(host, "rth_capi.cpp"),
                                     "-L" + os.path.dirname(cuda), "-lrtc_cuda", "-Wl,-rpath,$ORIGIN/../csrc"])
+    # the reference's `render_scene <scene-file> <output-file>` binary over the same library
+    exe = os.path.join(host, "render_scene")
+    if force or _newer(exe, srcs + [out]):
+        _run(["g++", "-O2", "-std=c++17", "-Wall", "-Wextra", "-o", exe, os.path.join(host, "render_scene.cpp"),
+              "-L" + host, "-lrth_host", "-L" + os.path.dirname(cuda), "-lrtc_cuda",
+              "-Wl,-rpath,$ORIGIN", "-Wl,-rpath,$ORIGIN/../csrc"])
     return out
 
 

@@ -396,6 +396,23 @@ int rtc_scene_finish(rtc_scene* s, void* stream_, rtc_stats* stats) {
   return rc;
 }
 
+// Device canvas of at least `need` doubles for this scene (recycled through the per-device pool).
+static int ensure_canvas(rtc_scene* s, size_t need) {
+  if (s->canvas_doubles >= need) return RTC_OK;
+  if (s->d_canvas) g_canvas_pool.give(s->device, s->d_canvas, s->canvas_doubles);
+  s->d_canvas = nullptr;
+  s->canvas_doubles = 0;
+  size_t got = 0;
+  s->d_canvas = g_canvas_pool.take(s->device, need, got);
+  if (s->d_canvas) {
+    s->canvas_doubles = got;
+  } else {
+    CUDA_TRY(cudaMalloc((void**)&s->d_canvas, need * sizeof(double)));
+    s->canvas_doubles = need;
+  }
+  return RTC_OK;
+}
+
 int rtc_render(rtc_scene* s, const rtc_camera* camera, const rtc_opts* opts, double* rgb_host, rtc_stats* stats) {
   if (!s || !rgb_host) return fail(RTC_ERR_INVALID, "NULL scene or canvas");
   auto t0 = std::chrono::steady_clock::now();
@@ -426,19 +443,8 @@ int rtc_render(rtc_scene* s, const rtc_camera* camera, const rtc_opts* opts, dou
     }
     cudaGetLastError();  // pageable memory: not an error, take the staged path
   }
-  if (s->canvas_doubles < need) {
-    if (s->d_canvas) g_canvas_pool.give(s->device, s->d_canvas, s->canvas_doubles);
-    s->d_canvas = nullptr;
-    s->canvas_doubles = 0;
-    size_t got = 0;
-    s->d_canvas = g_canvas_pool.take(s->device, need, got);
-    if (s->d_canvas) {
-      s->canvas_doubles = got;
-    } else {
-      CUDA_TRY(cudaMalloc((void**)&s->d_canvas, need * sizeof(double)));
-      s->canvas_doubles = need;
-    }
-  }
+  rc = ensure_canvas(s, need);
+  if (rc) return rc;
   s->launches = 0;
   const size_t row_doubles = (size_t)cam.hsize * 3;
   if (P.nranks <= 1) {
@@ -475,6 +481,45 @@ int rtc_quantize_device(int device, const double* rgb_dev, size_t n, uint8_t* rg
   quantize_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(rgb_dev, n, rgb8_dev);
   CUDA_TRY(cudaGetLastError());
   return RTC_OK;
+}
+
+// File-output path: render, quantise on the device, and move 3 B per pixel instead of 24.
+int rtc_render_rgb8(rtc_scene* s, const rtc_camera* camera, const rtc_opts* opts, uint8_t* rgb8_host, rtc_stats* stats) {
+  if (!s || !rgb8_host) return fail(RTC_ERR_INVALID, "NULL scene or image");
+  auto t0 = std::chrono::steady_clock::now();
+  CameraD cam;
+  RenderParams P;
+  bool faithful = false;
+  int rc = make_camera(camera, cam);
+  if (rc) return rc;
+  rc = make_params(camera, opts, P, faithful);
+  if (rc) return rc;
+  if (P.nranks > 1) return fail(RTC_ERR_INVALID, "rtc_render_rgb8 renders whole row ranges (nranks must be 1)");
+  CUDA_TRY(cudaSetDevice(s->device));
+  const size_t need = (size_t)cam.hsize * cam.vsize * 3;
+  rc = ensure_canvas(s, need);
+  if (rc) return rc;
+  s->launches = 0;
+  rc = launch_frame(s, cam, P, faithful, s->d_canvas, s->stream);
+  if (rc) return rc;
+  const size_t off = (size_t)P.row_begin * cam.hsize * 3, cnt = (size_t)(P.row_end - P.row_begin) * cam.hsize * 3;
+  if (cnt) {
+    uint8_t* d8 = nullptr;
+    CUDA_TRY(cudaMallocAsync((void**)&d8, cnt, s->stream));
+    rc = rtc_quantize_device(s->device, s->d_canvas + off, cnt, d8, s->stream);
+    if (rc == RTC_OK) {
+      s->launches++;
+      cudaError_t e = cudaMemcpyAsync(rgb8_host + off, d8, cnt, cudaMemcpyDeviceToHost, s->stream);
+      if (e != cudaSuccess) rc = fail(RTC_ERR_CUDA, cudaGetErrorString(e));
+    }
+    cudaFreeAsync(d8, s->stream);
+    if (rc) return rc;
+  }
+  rtc_stats local;
+  rc = rtc_scene_finish(s, s->stream, &local);
+  local.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  if (stats) *stats = local;
+  return rc;
 }
 
 int rtc_trace_rays(rtc_scene* s, size_t n, const double* origins, const double* directions, uint32_t remaining,

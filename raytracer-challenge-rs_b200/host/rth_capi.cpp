@@ -3,14 +3,17 @@
 // rth_render = `Camera::render(&World) -> Canvas` (camera.rs:133) on the GPU:
 //     flatten(World) → rtc_scene_create → rtc_render → rtc_scene_destroy      (include/rtc.h)
 // There is no CPU render path in this library.
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <fstream>
 #include <string>
+#include <vector>
 
 #include "rth_flatten.hpp"
 #include "rth_obj.hpp"
+#include "rth_yaml.hpp"
 
 using namespace rth;
 
@@ -28,7 +31,7 @@ extern "C" {
 struct rth_material {  // same layout as the oracle's C API so one Python struct serves both
   double color[3];
   double ambient, diffuse, specular, shininess, reflective, transparency, refractive_index;
-  int32_t has_pattern;
+  int32_t has_pattern;   // bit 0: material has a pattern; bit 1: the pattern had set_transform called
   int32_t pattern_kind;
   double pattern_a[3], pattern_b[3];
   double pattern_transform[16];
@@ -98,7 +101,7 @@ int rth_shape_set_material(void* s, const rth_material* m) {
     if (m->has_pattern) {
       Pattern p = make_pattern(m->pattern_kind, m->pattern_a[0], m->pattern_a[1], m->pattern_a[2], m->pattern_b[0],
                                m->pattern_b[1], m->pattern_b[2]);
-      p.set_transform(Mat4::from(m->pattern_transform));
+      if (m->has_pattern & 2) p.set_transform(Mat4::from(m->pattern_transform));  // bit 1: set_transform was called
       mat.set_pattern(p);
     }
     ((Shape*)s)->set_material(mat);
@@ -119,6 +122,22 @@ void* rth_obj_parse(const char* text, size_t len) {
     p.parse(text, len);
     return p.as_group().release();
   } catch (const std::exception& e) { fail(e.what()); return nullptr; }
+}
+
+// SceneParser::load_file (scene-parser/src/lib.rs:90-119). On success *world_out owns the World
+// (rth_world_free) and *camera_out the Camera (rth_camera_free; NULL when the file adds none — the
+// reference panics only later, at render, lib.rs:273). flags bit 0: accept the extended `add:` kinds
+// (cylinder, cone, group, csg, obj); base_dir (may be NULL): where relative `obj` file paths start.
+int rth_yaml_load(const char* text, size_t len, uint32_t flags, const char* base_dir, void** world_out,
+                  void** camera_out, int* skipped) {
+  try {
+    std::unique_ptr<YamlScene> sc =
+        load_yaml_scene(std::string(text, len), (flags & 1u) != 0, base_dir ? std::string(base_dir) : std::string());
+    if (skipped) *skipped = sc->skipped;
+    *camera_out = sc->camera.release();
+    *world_out = new World(std::move(sc->world));
+    return 0;
+  } catch (const std::exception& e) { return fail(e.what()); }
 }
 
 void* rth_world_new() { return new World(); }
@@ -144,6 +163,15 @@ void rth_camera_params(void* c, double* out) {
   out[0] = cam->pixel_size; out[1] = cam->half_width; out[2] = cam->half_height;
   std::memcpy(out + 3, cam->transform_inverse.m, 16 * sizeof(double));
 }
+void rth_camera_dims(void* c, size_t* hsize, size_t* vsize, double* fov) {
+  const Camera* cam = (const Camera*)c;
+  *hsize = cam->hsize; *vsize = cam->vsize; *fov = cam->field_of_view;
+}
+void rth_world_counts(void* w, size_t* n_objects, size_t* n_lights) {
+  *n_objects = ((World*)w)->objects.size();
+  *n_lights = ((World*)w)->lights.size();
+}
+void* rth_world_object(void* w, size_t i) { return ((World*)w)->objects.at(i).get(); }
 void rth_camera_to_rtc(void* c, rtc_camera* out) { *out = ((Camera*)c)->to_rtc(); }
 
 // ---- flattener --------------------------------------------------------------------------------
@@ -237,5 +265,126 @@ int rth_save_ppm(const double* rgb, size_t width, size_t height, const char* pat
   f.write(s.data(), (std::streamsize)s.size());
   return f ? 0 : fail("write failed");
 }
+
+// ---- 8-bit image files (image/png.rs:13-31; binary PPM) -------------------------------------------
+// Both take already quantised pixels (rtc_render_rgb8 / rtc_quantize_device / rth_quantize).
+int rth_save_p6(const uint8_t* rgb8, size_t width, size_t height, const char* path) {
+  std::ofstream f(path, std::ios::binary);
+  if (!f) return fail(std::string("cannot open ") + path);
+  char head[64];
+  int n = std::snprintf(head, sizeof head, "P6\n%zu %zu\n255\n", width, height);
+  f.write(head, n);
+  f.write((const char*)rgb8, (std::streamsize)(width * height * 3));
+  return f ? 0 : fail("write failed");
+}
+
+namespace {
+struct Crc32 {
+  uint32_t table[256];
+  Crc32() {
+    for (uint32_t i = 0; i < 256; i++) {
+      uint32_t c = i;
+      for (int k = 0; k < 8; k++) c = (c & 1u) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
+      table[i] = c;
+    }
+  }
+  uint32_t run(uint32_t crc, const uint8_t* p, size_t n) const {
+    for (size_t i = 0; i < n; i++) crc = table[(crc ^ p[i]) & 0xFFu] ^ (crc >> 8);
+    return crc;
+  }
+};
+void put_be32(std::string& s, uint32_t v) {
+  for (int k = 3; k >= 0; k--) s.push_back((char)((v >> (8 * k)) & 0xFFu));
+}
+void png_chunk(std::string& out, const char type[4], const std::string& data) {
+  static const Crc32 crc;
+  put_be32(out, (uint32_t)data.size());
+  std::string body(type, 4);
+  body += data;
+  out += body;
+  put_be32(out, crc.run(0xFFFFFFFFu, (const uint8_t*)body.data(), body.size()) ^ 0xFFFFFFFFu);
+}
+}  // namespace
+
+// 8-bit RGB PNG, filter 0 on every row, zlib stream of stored (uncompressed) deflate blocks: any PNG
+// reader decodes it to exactly the bytes handed in, which is all the parity contract asks of the file.
+int rth_save_png(const uint8_t* rgb8, size_t width, size_t height, const char* path) {
+  if (width == 0 || height == 0 || width > 0x7FFFFFFFu || height > 0x7FFFFFFFu) return fail("bad image size");
+  std::string raw;
+  raw.reserve(height * (width * 3 + 1));
+  for (size_t y = 0; y < height; y++) {
+    raw.push_back(0);
+    raw.append((const char*)rgb8 + y * width * 3, width * 3);
+  }
+  std::string z("\x78\x01", 2);
+  uint32_t a = 1, b = 0;  // adler32
+  for (size_t off = 0; off < raw.size();) {
+    size_t n = std::min<size_t>(65535, raw.size() - off);
+    z.push_back(off + n == raw.size() ? 1 : 0);
+    z.push_back((char)(n & 0xFF)); z.push_back((char)(n >> 8));
+    z.push_back((char)(~n & 0xFF)); z.push_back((char)((~n >> 8) & 0xFF));
+    z.append(raw, off, n);
+    for (size_t i = 0; i < n; i++) {
+      a += (uint8_t)raw[off + i];
+      if (a >= 65521) a -= 65521;
+      b += a;
+      if (b >= 65521) b -= 65521;
+    }
+    off += n;
+  }
+  put_be32(z, (b << 16) | a);
+  std::string out("\x89PNG\r\n\x1a\n", 8), ihdr;
+  put_be32(ihdr, (uint32_t)width);
+  put_be32(ihdr, (uint32_t)height);
+  ihdr += std::string("\x08\x02\x00\x00\x00", 5);  // 8 bit, colour type 2 (RGB), deflate, filter 0, no interlace
+  png_chunk(out, "IHDR", ihdr);
+  png_chunk(out, "IDAT", z);
+  png_chunk(out, "IEND", std::string());
+  std::ofstream f(path, std::ios::binary);
+  if (!f) return fail(std::string("cannot open ") + path);
+  f.write(out.data(), (std::streamsize)out.size());
+  return f ? 0 : fail("write failed");
+}
+
+// render_scene <scene-file> <output-file> (scene-parser/src/bin/render_scene.rs + lib.rs:90-119,263-283)
+// on the GPU: load the YAML, flatten, upload, render with 8-bit output, write .png / .ppm (P3, the
+// reference's PPM) / anything else as binary P6. flags bit 0: extended `add:` kinds; aa: samples.
+int rth_render_scene_file(const char* scene_path, const char* out_path, uint32_t flags, uint32_t aa, int device,
+                          rtc_stats* stats) {
+  try {
+    std::ifstream in(scene_path, std::ios::binary);
+    if (!in) return fail(std::string("cannot open ") + scene_path);
+    std::string text((std::istreambuf_iterator<char>(in)), std::istreambuf_iterator<char>());
+    std::string dir(scene_path);
+    size_t slash = dir.find_last_of('/');
+    dir = slash == std::string::npos ? std::string(".") : dir.substr(0, slash);
+    std::unique_ptr<YamlScene> sc = load_yaml_scene(text, (flags & 1u) != 0, dir);
+    if (!sc->camera) return fail("the scene adds no camera");  // the reference unwraps None at lib.rs:273
+    FlatScene flat = flatten(sc->world);
+    rtc_scene_desc d = flat.desc();
+    rtc_scene* scene = nullptr;
+    int rc = rtc_scene_create(&d, device, &scene);
+    if (rc) return fail(std::string("rtc_scene_create: ") + rtc_last_error()), rc;
+    rtc_camera cam = sc->camera->to_rtc();
+    rtc_opts o;
+    std::memset(&o, 0, sizeof o);
+    o.aa_samples = aa ? aa : 1; o.max_depth = 5; o.nranks = 1;
+    std::vector<uint8_t> img((size_t)cam.hsize * cam.vsize * 3);
+    rc = rtc_render_rgb8(scene, &cam, &o, img.data(), stats);
+    std::string msg = rc ? rtc_last_error() : "";
+    rtc_scene_destroy(scene);
+    if (rc) return fail("rtc_render_rgb8: " + msg), rc;
+    std::string out(out_path);
+    auto ends = [&](const char* e) { std::string s(e); return out.size() >= s.size() && out.compare(out.size() - s.size(), s.size(), s) == 0; };
+    if (ends(".png")) return rth_save_png(img.data(), cam.hsize, cam.vsize, out_path);
+    if (ends(".ppm")) {
+      std::vector<double> rgb(img.size());
+      for (size_t i = 0; i < img.size(); i++) rgb[i] = img[i] / 255.0;  // quant(v/255*255) == v for v in 0..255
+      return rth_save_ppm(rgb.data(), cam.hsize, cam.vsize, out_path);
+    }
+    return rth_save_p6(img.data(), cam.hsize, cam.vsize, out_path);
+  } catch (const std::exception& e) { return fail(e.what()); }
+}
+
 
 }  // extern "C"
