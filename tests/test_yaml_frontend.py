@@ -256,7 +256,7 @@ def test_gpu_yaml_scene_matches_oracle(pkg, prod, orc):
     wo, co = build_by_hand(orc.api)
     want, iw = orc.render(co, wo)
     got, stats, _ = pkg.render(cy, wy)
-    assert stats.rays() == iw["rays"]
+    assert stats.rays == iw["rays"]
     frac, max8, lin = compare_images(got, want, orc.quantize)
     assert frac >= 0.999 and max8 <= 1 and lin <= 1e-6
 
@@ -409,7 +409,7 @@ def test_gpu_render_scene_file_and_rgb8(pkg, prod, orc, tmp_path):
     st = pkg.render_scene_file(tmp_path / "scene.yml", tmp_path / "out.png", extended=True)
     wo, co = build_extended_by_hand(orc.api)
     want, iw = orc.render(co, wo)
-    assert st.rays() == iw["rays"]
+    assert st.rays == iw["rays"]
     got8 = _read_png(tmp_path / "out.png")
     want8 = orc.quantize(want)
     diff = np.abs(got8.astype(np.int16) - want8.astype(np.int16))
