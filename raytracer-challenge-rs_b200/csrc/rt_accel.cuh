@@ -110,9 +110,14 @@ RTC_HD bool own_box(double lx, double ly, double lz, double hx, double hy, doubl
 // correctly rounded quotient strictly beyond the limit (the tie t == limit is never filtered).
 RTC_HD bool quot_unwanted(const Query& C, double num, double den) {
   if (!(den > 0.0) || !(den < 1e150)) return false;
+#if defined(RTK_QUERY_BRANCHY)
   if (C.mode == Q_NEG) return num > 1e-150;
   if (num < -1e-150) return true;
   return num > C.limit * den * (1.0 + 1e-9);
+#else
+  const double wrong_side = C.mode == Q_NEG ? -num : num;  // Q_NEG wants t < 0 (its limit is +inf)
+  return (wrong_side < -1e-150) | (num > C.limit * den * (1.0 + 1e-9));
+#endif
 }
 
 // World::intersect → query. FAITHFUL: the reference's own search order, node by node (walk_range

@@ -196,9 +196,10 @@ RTC_HD MatD load_material(const SceneView& S, int32_t m) {
 }
 
 // Material::lighting (material.rs:38-82); `color` is the pattern/material colour at over_point.
-RTC_HD V3 lighting(const MatD& m, V3 color, V3 light_pos, V3 light_int, V3 point, V3 eyev, V3 normalv, bool in_shadow) {
+// `lightv` = (light.position - point).normalize() (material.rs:52) is handed in: it is, bit for bit,
+// the direction of the shadow ray is_shadowed built for the same point and light (world.rs:96-99).
+RTC_HD V3 lighting(const MatD& m, V3 color, V3 lightv, V3 light_int, V3 eyev, V3 normalv, bool in_shadow) {
   V3 effective = color * light_int;
-  V3 lightv = normalize(light_pos - point);
   V3 ambient = effective * m.ambient;
   if (in_shadow) return ambient;
   double ldn = dot(lightv, normalv);
@@ -208,8 +209,17 @@ RTC_HD V3 lighting(const MatD& m, V3 color, V3 light_pos, V3 light_int, V3 point
     V3 reflectv = reflect(-lightv, normalv);
     double rde = dot(reflectv, eyev);
     if (!(rde <= 0.0)) {
-      double factor = pow(rde, m.shininess);
-      specular = light_int * m.specular * factor;
+      // specular 0 (matte walls and floors): light_int * 0 * factor is the signed zero light_int * 0 for any
+      // finite factor >= 0, and 0 < rde <= 2, 0 <= shininess <= 1000 bounds pow to (0, 2^1000]
+#if !defined(RTK_NO_POWSKIP)
+      if (m.specular == 0.0 && rde <= 2.0 && m.shininess >= 0.0 && m.shininess <= 1000.0) {
+        specular = light_int * m.specular;
+      } else
+#endif
+      {
+        double factor = pow(rde, m.shininess);
+        specular = light_int * m.specular * factor;
+      }
     }
   }
   return ambient + diffuse + specular;
@@ -232,33 +242,42 @@ RTC_HD double schlick(const Comps& c) {
   return r0 + (1.0 - r0) * (x * x4);
 }
 
-// One level of the color_at recursion. Lives in LOCAL memory (dynamically indexed array): all the
-// state of the hit being shaded that is not needed INSIDE a search is parked here, so the search
-// loop runs with few live registers (more resident warps hide the FP64 latency).
+// A suspended shade_hit: what a level of the color_at recursion needs once the colour of its
+// reflection / refraction child comes back. Lives in LOCAL memory (dynamically indexed array) and is
+// written once, when the level descends — 128 bytes per level, so the levels a thread really uses
+// stay in L1. Everything else about the hit being shaded is transient and lives in Tracer::cur.
 struct Frame {
-  RayD ray;        // the ray color_at is being evaluated for at this level
-  V3 point, over_point, normalv;  // of the hit being shaded (eyev = -ray.d, under_point and reflectv are re-derived)
-  V3 color;        // pattern / material colour at over_point
-  V3 surface;      // Σ lights
-  V3 reflected;    // reflected_color result
-  RayD refr_ray;   // pending refraction ray
+  V3 surface;      // Σ lighting(...) over the lights (shade_hit's `surface`, world.rs:41-58)
+  V3 reflected;    // reflected_color once known
+  RayD refr_ray;   // the refraction ray, valid if need_refract
   double reflective, transparency, reflectance;
-  int32_t node, mat;
-  uint8_t state;   // 1: waiting for reflection child, 2: waiting for refraction child
-  uint8_t need_refract, use_schlick, want_reflect, want_refract, _pad[3];
+  int32_t state;   // 1: waiting for reflection child, 2: waiting for refraction child
+  uint32_t bits;   // FR_*
 };
+enum : uint32_t { FR_NEED_REFRACT = 1u, FR_USE_SCHLICK = 2u };
 
-RTC_HD V3 combine(const Frame& f, V3 refracted) {  // world.rs:62-67
-  return f.use_schlick ? f.surface + f.reflected * f.reflectance + refracted * (1.0 - f.reflectance)
-                       : f.surface + f.reflected + refracted;
+// world.rs:62-67
+RTC_HD V3 combine(V3 surface, V3 reflected, V3 refracted, double reflectance, bool use_schlick) {
+  return use_schlick ? surface + reflected * reflectance + refracted * (1.0 - reflectance)
+                     : surface + reflected + refracted;
 }
+
+// The hit being shaded at the current level, from the closest-hit answer until the level descends or
+// returns. One copy serves every level: a parent's copy is dead once its child starts.
+struct Shading {
+  RayD ray;        // the ray color_at is being evaluated for at this level
+  V3 point, over_point, normalv;  // eyev = -ray.d, under_point and reflectv are re-derived
+  V3 color;        // pattern / material colour at over_point
+  V3 surface;
+  int32_t node, mat;
+};
 
 // World::color_at(ray, remaining = max_depth) (world.rs:70-81) with shade_hit, is_shadowed,
 // reflected_color and refracted_color (world.rs:40-134) as ONE state machine around ONE search
 // site: every closest-hit, shadow (world.rs:95-105) and containers query of the whole recursion
 // tree is put to the same search, in the reference's evaluation order. The caller loops
 //     tr.start(ray, depth);  for (;;) { search(S, tr.qray, tr.q, ...);  if (tr.advance(S, ...)) break; }
-// so that a persistent kernel can keep every lane of a warp at that one search site, whatever
+// so the (large) search code exists once per kernel and a warp stays converged on it whatever
 // pixel, recursion depth or phase each lane is in.
 enum : int { PH_CLOSEST = 0, PH_SHADOW = 1, PH_NEG = 2 };
 enum : int { NX_RETURN = 0, NX_SHADOW = 1, NX_LIT = 2, NX_N1N2 = 3 };
@@ -266,12 +285,14 @@ enum : int { NX_RETURN = 0, NX_SHADOW = 1, NX_LIT = 2, NX_N1N2 = 3 };
 struct Tracer {
   RayD qray;       // the ray of the pending query
   Query q;
+  Shading cur;
   V3 result;
   double t_primary;
   int sp, remaining, li, phase;
 
   RTC_HD void start(const RayD& r, int max_depth, Frame* frames, uint32_t* err) {
-    frames[0].ray = r;
+    (void)frames;
+    cur.ray = r;
     qray = r;
     sp = 0;
     remaining = max_depth;
@@ -287,7 +308,6 @@ struct Tracer {
     int next;
     V3 res = v3(0.0, 0.0, 0.0);
     double n1 = -1.0, n2 = -1.0;
-    Frame& f = frames[sp];
     if (phase == PH_CLOSEST) {
       if (sp == 0) t_primary = q.node >= 0 ? q.limit : -1.0;
       if (q.node < 0) {
@@ -296,37 +316,36 @@ struct Tracer {
       } else {
         rtc_node nd = load_node(S.nodes + q.node);
         Comps c;
-        prepare(S, f.ray, q.limit, q.node, nd, c);
-        f.point = c.point;
-        f.over_point = c.over_point;
-        f.normalv = c.normalv;
-        f.node = q.node;
-        f.mat = nd.material;
+        prepare(S, cur.ray, q.limit, q.node, nd, c);
+        cur.point = c.point;
+        cur.over_point = c.over_point;
+        cur.normalv = c.normalv;
+        cur.node = q.node;
+        cur.mat = nd.material;
         const rtc_material* M = S.materials + nd.material;
         const int32_t pat = RTC_LDG(&M->pattern);
         const double* leaf_inv = S.xforms + 12 * (size_t)nd.xform;
-        f.color = pat >= 0 ? pattern_color(S, pat, leaf_inv, c.over_point)
-                           : v3(RTC_LDG(&M->color[0]), RTC_LDG(&M->color[1]), RTC_LDG(&M->color[2]));
-        f.surface = v3(0.0, 0.0, 0.0);  // shade_hit: Σ lighting in light order from (0,0,0), world.rs:41-58
+        cur.color = pat >= 0 ? pattern_color(S, pat, leaf_inv, c.over_point)
+                             : v3(RTC_LDG(&M->color[0]), RTC_LDG(&M->color[1]), RTC_LDG(&M->color[2]));
+        cur.surface = v3(0.0, 0.0, 0.0);  // shade_hit: Σ lighting in light order from (0,0,0), world.rs:41-58
         li = 0;
         next = S.n_lights > 0 ? NX_SHADOW : NX_LIT;
       }
     } else if (phase == PH_SHADOW) {
       const rtc_light* L = S.lights + li;
-      V3 lp = v3(RTC_LDG(&L->position[0]), RTC_LDG(&L->position[1]), RTC_LDG(&L->position[2]));
       V3 lint = v3(RTC_LDG(&L->intensity[0]), RTC_LDG(&L->intensity[1]), RTC_LDG(&L->intensity[2]));
-      const MatD m = load_material(S, f.mat);
-      f.surface = f.surface + lighting(m, f.color, lp, lint, f.over_point, -f.ray.d, f.normalv, q.done());
+      const MatD m = load_material(S, cur.mat);
+      cur.surface = cur.surface + lighting(m, cur.color, qray.d, lint, -cur.ray.d, cur.normalv, q.done());
       li++;
       next = li < S.n_lights ? NX_SHADOW : NX_LIT;
     } else {
-      containers_n1n2(S, neg, f.node, n1, n2, err);
+      containers_n1n2(S, neg, cur.node, n1, n2, err);
       next = NX_N1N2;
     }
     if (next == NX_SHADOW) {  // World::is_shadowed(over_point, light li), world.rs:95-105
       const rtc_light* L = S.lights + li;
       V3 lp = v3(RTC_LDG(&L->position[0]), RTC_LDG(&L->position[1]), RTC_LDG(&L->position[2]));
-      const V3 op = f.over_point;
+      const V3 op = cur.over_point;
       V3 v = lp - op;
       double distance = magnitude(v);
       qray.o = op;
@@ -339,60 +358,65 @@ struct Tracer {
     bool descend = false;
     RayD child;
     child.o = child.d = v3(0.0, 0.0, 0.0);
-    if (next == NX_LIT) {
-      const rtc_material* M = S.materials + f.mat;
+    if (next == NX_LIT || next == NX_N1N2) {
+      // the material's reflective / transparency decide what this level still needs (re-read after a
+      // containers query rather than carried through it)
+      const rtc_material* M = S.materials + cur.mat;
       const double reflective = RTC_LDG(&M->reflective), transparency = RTC_LDG(&M->transparency);
-      f.reflective = reflective;
-      f.transparency = transparency;
-      f.want_reflect = !(feq(reflective, 0.0) || remaining == 0);    // world.rs:108
-      f.want_refract = !(feq(transparency, 0.0) || remaining == 0);  // world.rs:117
-      f.use_schlick = (reflective > 0.0 && transparency > 0.0) ? 1 : 0;  // world.rs:62
-      f.need_refract = 0;
-      f.reflectance = 0.0;
-      if (f.want_refract || f.use_schlick) {
+      const bool want_reflect = !(feq(reflective, 0.0) || remaining == 0);    // world.rs:108
+      const bool want_refract = !(feq(transparency, 0.0) || remaining == 0);  // world.rs:117
+      const bool use_schlick = reflective > 0.0 && transparency > 0.0;        // world.rs:62
+      if (next == NX_LIT && (want_refract || use_schlick)) {
         // n1/n2 are only ever consumed by refracted_color and schlick
-        qray = f.ray;
+        qray = cur.ray;
         q.init_neg(&neg, err);
         phase = PH_NEG;
         return false;
       }
-      next = NX_N1N2;
-    }
-    if (next == NX_N1N2) {
-      const V3 rd = f.ray.d, normalv = f.normalv;
+      const V3 rd = cur.ray.d, normalv = cur.normalv;
       const V3 eyev = -rd;
-      if (f.use_schlick) {
+      double reflectance = 0.0;
+      bool need_refract = false;
+      RayD refr;
+      refr.o = refr.d = v3(0.0, 0.0, 0.0);
+      if (use_schlick) {
         Comps c;
         c.eyev = eyev; c.normalv = normalv; c.n1 = n1; c.n2 = n2;
-        f.reflectance = schlick(c);
+        reflectance = schlick(c);
       }
-      if (f.want_refract) {  // world.rs:121-131
+      if (want_refract) {  // world.rs:121-131
         double n_ratio = n1 / n2;
         double cos_i = dot(eyev, normalv);
         double sin2_t = n_ratio * n_ratio * (1.0 - cos_i * cos_i);
         if (!(sin2_t > 1.0)) {
           double cos_t = sqrt(1.0 - sin2_t);
-          f.refr_ray.o = f.point - normalv * EPS;  // under_point, intersection.rs:99
-          f.refr_ray.d = normalv * (n_ratio * cos_i - cos_t) - eyev * n_ratio;  // not normalised
-          f.need_refract = 1;
+          refr.o = cur.point - normalv * EPS;  // under_point, intersection.rs:99
+          refr.d = normalv * (n_ratio * cos_i - cos_t) - eyev * n_ratio;  // not normalised
+          need_refract = true;
         }
       }
-      if (f.want_reflect) {
-        rc.reflect++;
-        f.state = 1;
-        child.o = f.over_point;
-        child.d = reflect(rd, normalv);  // reflectv, intersection.rs:100
-        descend = true;
-      } else {
+      if (want_reflect || need_refract) {
+        Frame& f = frames[sp];
+        f.surface = cur.surface;
         f.reflected = v3(0.0, 0.0, 0.0);
-        if (f.need_refract) {
+        f.refr_ray = refr;
+        f.reflective = reflective;
+        f.transparency = transparency;
+        f.reflectance = reflectance;
+        f.bits = (need_refract ? FR_NEED_REFRACT : 0u) | (use_schlick ? FR_USE_SCHLICK : 0u);
+        if (want_reflect) {
+          rc.reflect++;
+          f.state = 1;
+          child.o = cur.over_point;
+          child.d = reflect(rd, normalv);  // reflectv, intersection.rs:100
+        } else {
           rc.refract++;
           f.state = 2;
-          child = f.refr_ray;
-          descend = true;
-        } else {
-          res = combine(f, v3(0.0, 0.0, 0.0));
+          child = refr;
         }
+        descend = true;
+      } else {
+        res = combine(cur.surface, v3(0.0, 0.0, 0.0), v3(0.0, 0.0, 0.0), reflectance, use_schlick);
       }
     }
     // ---- return `res` to the parents --------------------------------------------------------------
@@ -401,23 +425,25 @@ struct Tracer {
       sp--;
       remaining++;
       Frame& p = frames[sp];
+      const uint32_t bits = p.bits;
       if (p.state == 1) {
-        p.reflected = res * p.reflective;  // world.rs:113
-        if (p.need_refract) {
+        const V3 reflected = res * p.reflective;  // world.rs:113
+        if (bits & FR_NEED_REFRACT) {
+          p.reflected = reflected;
           rc.refract++;
           p.state = 2;
           child = p.refr_ray;
           descend = true;
         } else {
-          res = combine(p, v3(0.0, 0.0, 0.0));
+          res = combine(p.surface, reflected, v3(0.0, 0.0, 0.0), p.reflectance, (bits & FR_USE_SCHLICK) != 0);
         }
       } else {
-        res = combine(p, res * p.transparency);  // world.rs:133
+        res = combine(p.surface, p.reflected, res * p.transparency, p.reflectance, (bits & FR_USE_SCHLICK) != 0);  // world.rs:133
       }
     }
     sp++;
     remaining--;
-    frames[sp].ray = child;
+    cur.ray = child;
     qray = child;
     q.init_closest(err);
     phase = PH_CLOSEST;

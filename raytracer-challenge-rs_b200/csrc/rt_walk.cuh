@@ -55,13 +55,23 @@ struct Query {
 
   RTC_HD void init_closest(uint32_t* e) { mode = Q_CLOSEST; limit = rt_inf(); node = -1; list = nullptr; err = e; }
   RTC_HD void init_shadow(double distance, uint32_t* e) { mode = Q_SHADOW; limit = distance; node = 0; list = nullptr; err = e; }
-  RTC_HD void init_neg(HitList* l, uint32_t* e) { mode = Q_NEG; limit = 0.0; node = -1; list = l; l->n = 0; err = e; }
+  RTC_HD void init_neg(HitList* l, uint32_t* e) { mode = Q_NEG; limit = rt_inf(); node = -1; list = l; l->n = 0; err = e; }
 
-  // would the reference's sorted list hand this intersection to the caller?
+  // would the reference's sorted list hand this intersection to the caller? One branch-free form for
+  // the three modes (lanes of a warp are in different modes): the sign test flips for Q_NEG, whose
+  // limit is +inf; the tie `t == limit` can only win in Q_CLOSEST (node is 0/1 in Q_SHADOW, -1 in
+  // Q_NEG, never above a node index); only Q_SHADOW asks for the has_shadow flag.
   RTC_HD bool want(double t, int32_t nd, uint32_t flags) const {
+#if defined(RTK_QUERY_BRANCHY)
     if (mode == Q_CLOSEST) return t >= 0.0 && (t < limit || (t == limit && nd < node));
     if (mode == Q_SHADOW) return t >= 0.0 && t < limit && (flags & RTC_FLAG_SHADOW);
     return t < 0.0;
+#else
+    const bool side = (t >= 0.0) != (mode == Q_NEG);
+    const bool within = (t < limit) | ((t == limit) & (nd < node));
+    const uint32_t need = mode == Q_SHADOW ? (uint32_t)RTC_FLAG_SHADOW : 0u;
+    return side & within & ((flags & need) == need) & (t == t);
+#endif
   }
   RTC_HD void take(double t, int32_t nd) {
     if (mode == Q_CLOSEST) { limit = t; node = nd; return; }
