@@ -216,6 +216,10 @@ RTC_API double* rtc_canvas_ptr(rtc_canvas* canvas);
 RTC_API int rtc_canvas_download(rtc_canvas* canvas, double* host, size_t offset_doubles, size_t n_doubles);
 RTC_API void rtc_canvas_destroy(rtc_canvas* canvas);
 
+/* Debug / known-answer entry: Vector::normalize (vector.rs:25-28) of n host vectors (xyz triples) on
+ * the device, through the same normalize() the kernels use (its divisions share one reciprocal). */
+RTC_API int rtc_debug_normalize(int device, size_t n, const double* xyz_host, double* out_host);
+
 /* Roofline denominator: measured FP64 throughput of `device` in GFLOP/s.
  * fused=1: dependent-chain-free DFMA stream (2 flops each); fused=0: alternating DADD/DMUL
  * (1 flop each) — the attainable roof for this library, which is built with --fmad=false. */

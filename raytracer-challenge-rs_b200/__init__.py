@@ -106,6 +106,7 @@ def cuda_lib():
         lib.rtc_canvas_destroy.argtypes = [vp]
         lib.rtc_canvas_destroy.restype = None
         lib.rtc_measure_fp64.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double)]
+        lib.rtc_debug_normalize.argtypes = [C.c_int, sz, pd, pd]
         _libs["cuda"] = lib
     return _libs["cuda"]
 

@@ -145,6 +145,16 @@ __global__ void shadow_kernel(SceneView S, V3 point, int light, int* __restrict_
   flush_counters(rc, err, counters);
 }
 
+// Known-answer kernel for the device normalize() (shared-reciprocal division, rt_math.cuh)
+__global__ void normalize_kernel(const double* __restrict__ xyz, size_t n, double* __restrict__ out) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    V3 r = normalize(v3(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]));
+    out[3 * i] = r.x; out[3 * i + 1] = r.y; out[3 * i + 2] = r.z;
+  }
+}
+
 // image/ppm.rs:73-75: (v * 255.0).round() as u8 — round half away from zero, saturating, NaN → 0
 __global__ void quantize_kernel(const double* __restrict__ rgb, size_t n, uint8_t* __restrict__ out) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -627,6 +627,23 @@ void rtc_canvas_destroy(rtc_canvas* c) {
   delete c;
 }
 
+int rtc_debug_normalize(int device, size_t n, const double* xyz_host, double* out_host) {
+  if (!xyz_host || !out_host) return fail(RTC_ERR_INVALID, "NULL buffer");
+  CUDA_TRY(cudaSetDevice(device));
+  if (n == 0) return RTC_OK;
+  double* d = nullptr;
+  CUDA_TRY(cudaMalloc((void**)&d, 2 * 3 * n * sizeof(double)));
+  cudaError_t e = cudaMemcpy(d, xyz_host, 3 * n * sizeof(double), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    normalize_kernel<<<(int)((n + 255) / 256 < 4096 ? (n + 255) / 256 : 4096), 256>>>(d, n, d + 3 * n);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(out_host, d + 3 * n, 3 * n * sizeof(double), cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (e != cudaSuccess) return fail(RTC_ERR_CUDA, cudaGetErrorString(e));
+  return RTC_OK;
+}
+
 int rtc_measure_fp64(int device, int fused, double* gflops_out) {
   if (!gflops_out) return fail(RTC_ERR_INVALID, "NULL out");
   CUDA_TRY(cudaSetDevice(device));

@@ -168,3 +168,28 @@ def test_pinned_canvas_is_written_zero_copy(pkg, prod):
     got = pinned.numpy()
     assert np.array_equal(got[40:100], staged[40:100]) and np.all(got[:40] == -7.0) and np.all(got[100:] == -7.0)
     ds.close()
+
+
+@pytest.mark.gpu
+def test_normalize_is_ieee_exact(pkg):
+    """The device normalize() divides three components by one magnitude through a shared refined
+    reciprocal (rt_math.cuh Divisor). Every quotient must be the correctly rounded IEEE one, i.e. what
+    numpy's float64 `/` gives for the same magnitude — over ordinary, tiny, huge, zero, denormal,
+    infinite and NaN inputs."""
+    rng = np.random.default_rng(2024)
+    parts = [rng.standard_normal((400000, 3)),
+             rng.standard_normal((200000, 3)) * np.exp2(rng.integers(-40, 40, size=(200000, 3))),
+             rng.standard_normal((50000, 3)) * np.exp2(rng.integers(-510, -480, size=(50000, 1))),   # squares underflow
+             rng.standard_normal((50000, 3)) * np.exp2(rng.integers(480, 510, size=(50000, 1))),     # squares near overflow
+             rng.integers(-3, 4, size=(50000, 3)).astype(np.float64),                                # exact zeros, small ints
+             np.array([[0, 0, 0], [0.0, -0.0, 1.0], [np.inf, 1, 1], [np.nan, 1, 2], [5e-324, 0, 0], [1e308, 1e308, 1e308],
+                       [1e-320, 1e-310, 0], [1, 2, 2], [3, 4, 0], [1e-160, 1e-160, 1e-160]], dtype=np.float64)]
+    v = np.ascontiguousarray(np.concatenate(parts))
+    out = np.empty_like(v)
+    assert pkg.cuda_lib().rtc_debug_normalize(0, len(v), v.ctypes.data, out.ctypes.data) == 0
+    with np.errstate(all="ignore"):
+        m = np.sqrt(v[:, 0] * v[:, 0] + v[:, 1] * v[:, 1] + v[:, 2] * v[:, 2])    # vector.rs:21, same order
+        want = v / m[:, None]
+    same = (out.view(np.uint64) == want.view(np.uint64)) | (np.isnan(out) & np.isnan(want))
+    bad = np.argwhere(~same)
+    assert len(bad) == 0, (len(bad), v[bad[:5, 0]], out[bad[:5, 0]], want[bad[:5, 0]])
