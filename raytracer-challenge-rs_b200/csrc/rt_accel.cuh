@@ -198,6 +198,7 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
           int32_t i, par;
           rtc_node nd;
           LeafHits hits;
+          bool generic = false;
           RTK_COUNT(prim_tests, 1);
           if (k < S.n_always) {  // (uniform per run) every-ray prim: one 128-byte record
             const PrimRec* rec = S.recs + k;
@@ -217,9 +218,7 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
             }
             lr = ray_transform_v2(rec->inv, ray);
             lr_xf = -1;
-            LeafHits h;
-            isect_leaf(S, nd, lr, h);
-            hits = h;
+            generic = true;
           } else {  // BVH prim: one 96-byte record, geometry inline (no node → triangle indirection)
             const LeafRec* lrec = S.leaf_recs + (k - S.n_always);
 #if defined(__CUDA_ARCH__)
@@ -242,10 +241,18 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
             hits.t0 = hits.t1 = hits.t2 = hits.t3 = 0.0;
             if (nd.kind == RTC_SPHERE) {
               isect_sphere(lr, [&](double t) { hits.push(t); });
-            } else {
+            } else if (nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE) {
               double t, u, v;
               if (isect_triangle(lr, lrec->g, t, u, v)) hits.push(t);
+            } else {  // cube, bounded cylinder
+              nd.aux = RTC_LDG(&lrec->aux);
+              generic = true;
             }
+          }
+          if (generic) {  // ONE isect_leaf site for every-ray prims and the BVH's non-triangle kinds
+            LeafHits h;
+            isect_leaf(S, nd, lr, h);
+            hits = h;
           }
           const LeafHits& h = hits;
 #if defined(__CUDACC__)

@@ -44,11 +44,11 @@ struct PrimRec {     // 128 bytes: everything the every-ray loop needs about one
   double inv[12];    // rows 0..2 of the leaf's transform_inverse (unused for a CSG prim)
 };
 
-struct LeafRec {     // 96 bytes: one BVH prim (triangle / smooth triangle / sphere), in BVH leaf order
+struct LeafRec {     // 96 bytes: one BVH prim (any bounded leaf shape), in BVH leaf order
   int32_t node, xform, parent;
   uint32_t kind_flags;   // kind << 24 | flags
-  double g[9];           // triangles: p1, e1, e2 (triangle.rs:14-21); spheres: unused
-  double _pad;
+  double g[9];           // triangles: p1, e1, e2 (triangle.rs:14-21); other kinds: unused
+  int32_t aux, _pad;     // rtc_node.aux (cylinder: index into limits)
 };
 
 static_assert(sizeof(PrimRec) == 128 && sizeof(LeafRec) == 96 && sizeof(BvhNode) == 128, "record layout");
@@ -123,9 +123,19 @@ inline bool leaf_world_box(const rtc_scene_desc* d, const rtc_node& nd, Box& out
     xf(fwd, p1, w); out.add(w);
     xf(fwd, p2, w); out.add(w);
     xf(fwd, p3, w); out.add(w);
-  } else if (nd.kind == RTC_SPHERE) {
+  } else if (nd.kind == RTC_SPHERE || nd.kind == RTC_CUBE || nd.kind == RTC_CYLINDER) {
+    // object-space extent: the unit box; a cylinder is radius 1 between its limits (cylinder.rs:27-40)
+    // — an unbounded one stays an every-ray prim. Cones are never admitted: for a ray parallel to a
+    // cone half (|a| < EPSILON) the reference emits t = -c/2·b without the y-limit test (cone.rs:100-108),
+    // a hit that can lie anywhere along the ray, so no box bounds a cone's intersections.
+    double r = 1.0, y0 = -1.0, y1 = 1.0;
+    if (nd.kind == RTC_CYLINDER) {
+      y0 = d->limits[2 * (size_t)nd.aux];
+      y1 = d->limits[2 * (size_t)nd.aux + 1];
+      if (!std::isfinite(y0) || !std::isfinite(y1) || !(y0 <= y1)) return false;
+    }
     for (int k = 0; k < 8; k++) {
-      double p[3] = {(k & 1) ? 1.0 : -1.0, (k & 2) ? 1.0 : -1.0, (k & 4) ? 1.0 : -1.0};
+      double p[3] = {(k & 1) ? r : -r, (k & 2) ? y1 : y0, (k & 4) ? r : -r};
       xf(fwd, p, w); out.add(w);
     }
   } else {
@@ -292,6 +302,7 @@ struct Builder {
       LeafRec& r = out.leaf_recs[(size_t)k];
       r.node = i; r.xform = nd.xform; r.parent = out.parent[(size_t)i];
       r.kind_flags = ((uint32_t)nd.kind << 24) | (nd.flags & 0xffffffu);
+      r.aux = nd.aux;
       if (nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE)
         for (int c = 0; c < 9; c++) r.g[c] = desc->tri_p1e1e2[9 * (size_t)nd.aux + c];
     }
@@ -349,7 +360,7 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
     } else {
       Prim p;
       p.node = i;
-      if ((nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE || nd.kind == RTC_SPHERE) && leaf_world_box(d, nd, p.box)) {
+      if (nd.kind != RTC_PLANE && leaf_world_box(d, nd, p.box)) {
         for (int a = 0; a < 3; a++) p.c[a] = 0.5 * (p.box.lo[a] + p.box.hi[a]);
         cand.push_back(p);
       } else {

@@ -45,8 +45,7 @@ RTC_HD void slab_axis(double origin, double direction, double mn, double mx, dou
   double tmax_numerator = mx - origin;
   double a, b;
   if (fabs(direction) >= EPS) {
-    a = tmin_numerator / direction;
-    b = tmax_numerator / direction;
+    divide2(tmin_numerator, tmax_numerator, direction, a, b);
   } else {
     a = tmin_numerator * rt_inf();
     b = tmax_numerator * rt_inf();
@@ -74,8 +73,8 @@ RTC_HD void isect_sphere(const RayD& r, Emit&& emit) {
   double disc = b * b - 4.0 * a * c;
   if (disc < 0.0) return;
   double sq = sqrt(disc);
-  double t1 = (-b - sq) / (2.0 * a);
-  double t2 = (-b + sq) / (2.0 * a);
+  double t1, t2;
+  divide2(-b - sq, -b + sq, 2.0 * a, t1, t2);
   emit(t1);
   emit(t2);
 }
@@ -102,12 +101,13 @@ RTC_HD void isect_cube(const RayD& r, Emit&& emit) {
 // cylinder.rs:48-65 / cone.rs:48-65 — note: no |d.y| < EPSILON guard; ±inf/NaN t fail check_cap.
 template <class Emit>
 RTC_HD void isect_caps(const RayD& r, double minimum, double maximum, bool cone, Emit&& emit) {
-  double t = (minimum - r.o.y) / r.d.y;
+  double t, tmax_cap;
+  divide2(minimum - r.o.y, maximum - r.o.y, r.d.y, t, tmax_cap);
   double x = r.o.x + t * r.d.x;
   double z = r.o.z + t * r.d.z;
   double rad2 = cone ? minimum * minimum : 1.0;
   if ((x * x + z * z) <= rad2) emit(t);
-  t = (maximum - r.o.y) / r.d.y;
+  t = tmax_cap;
   x = r.o.x + t * r.d.x;
   z = r.o.z + t * r.d.z;
   rad2 = cone ? maximum * maximum : 1.0;
@@ -126,8 +126,8 @@ RTC_HD void isect_cylinder(const RayD& r, double minimum, double maximum, bool c
   double disc = b * b - 4.0 * a * c;
   if (disc < 0.0) return;  // before the caps, as in the reference
   double sq = sqrt(disc);
-  double t0 = (-b - sq) / (2.0 * a);
-  double t1 = (-b + sq) / (2.0 * a);
+  double t0, t1;
+  divide2(-b - sq, -b + sq, 2.0 * a, t0, t1);
   double y0 = r.o.y + t0 * r.d.y;
   if (minimum < y0 && y0 < maximum) emit(t0);
   double y1 = r.o.y + t1 * r.d.y;
@@ -152,8 +152,8 @@ RTC_HD void isect_cone(const RayD& r, double minimum, double maximum, bool close
   double disc = b * b - 4.0 * a * c;
   if (disc < 0.0) return;
   double sq = sqrt(disc);
-  double t0 = (-b - sq) / (2.0 * a);
-  double t1 = (-b + sq) / (2.0 * a);
+  double t0, t1;
+  divide2(-b - sq, -b + sq, 2.0 * a, t0, t1);
   double y0 = r.o.y + t0 * r.d.y;
   if (minimum < y0 && y0 < maximum) emit(t0);
   double y1 = r.o.y + t1 * r.d.y;

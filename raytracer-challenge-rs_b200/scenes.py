@@ -352,6 +352,57 @@ def mesh_and_spheres(api, width=3840, height=2160, nx=1000, nz=500, n_spheres=20
     return w, cam
 
 
+def solids_field(api, width=640, height=360):
+    """Parity case for bounded solids in the BVH: a 6 x 4 field of cubes, cylinders and cones (open and
+    closed, rotated and scaled, some glass or mirrored, every third one inside a group) plus one
+    unbounded cylinder and one unbounded cone, which must stay every-ray prims."""
+    w = api.world()
+    w.add_light((-8, 10, -8), (1, 1, 1))
+    w.add_light((6, 4, -9), (0.3, 0.3, 0.4))
+    w.add_object(api.plane().set_material(Material(pattern=checkers_pattern((0.3, 0.3, 0.3), (0.7, 0.7, 0.7)), reflective=0.2)))
+    w.add_object(api.cylinder().set_transform(T.chain(T.scaling(0.2, 1, 0.2), T.translation(-7, 0, 6)))
+                 .set_material(Material(color=(0.9, 0.8, 0.1))))
+    w.add_object(api.cone().set_transform(T.chain(T.scaling(0.15, 0.6, 0.15), T.translation(7, 2, 6)))
+                 .set_material(Material(color=(0.1, 0.8, 0.9))))
+    glass = Material(color=(0.05, 0.05, 0.1), diffuse=0.2, specular=0.9, shininess=250, reflective=0.8,
+                     transparency=0.85, refractive_index=1.5)
+    k = 0
+    for ix in range(6):
+        for iz in range(4):
+            x, z = -5.0 + 2.0 * ix, -1.0 + 2.2 * iz
+            kind = k % 5
+            if kind == 0:
+                shape = api.cube()
+            elif kind == 1:
+                shape = api.cylinder(-0.5, 1.0, True)
+            elif kind == 2:
+                shape = api.cone(-1.0, 0.0, True)
+            elif kind == 3:
+                shape = api.cylinder(0.0, 1.5, False)
+            else:
+                shape = api.cone(-1.0, 0.5, False)
+            s = 0.35 + 0.07 * (k % 4)
+            shape.set_transform(T.chain(T.scaling(s, s * (1.0 + 0.2 * (k % 3)), s), T.rotation_z(0.11 * (k % 5)),
+                                        T.rotation_y(0.37 * k), T.translation(x, 1.0 + 0.15 * (k % 3), z)))
+            if k % 7 == 3:
+                shape.set_material(glass)
+            elif k % 4 == 1:
+                shape.set_material(Material(color=(0.2 + 0.1 * (k % 5), 0.3, 0.8 - 0.1 * (k % 6)), reflective=0.4))
+            else:
+                shape.set_material(Material(color=(0.9 - 0.1 * (k % 6), 0.4 + 0.1 * (k % 4), 0.2), shininess=30 + 10 * k))
+            if k % 3 == 2:
+                g = api.group()
+                g.add_child(shape)
+                g.set_transform(T.chain(T.rotation_y(0.05 * k), T.translation(0, 0.1, 0)))
+                w.add_object(g)
+            else:
+                w.add_object(shape)
+            k += 1
+    cam = api.camera(width, height, 1.0)
+    cam.set_transform(T.view_transform((0, 6, -11), (0, 0.5, 3), (0, 1, 0)))
+    return w, cam
+
+
 CONFIGS = {
     "default_world": default_world,
     "chapter7": chapter7,                # config 1
@@ -360,6 +411,7 @@ CONFIGS = {
     "primitives_csg": primitives_csg,    # config 3b
     "glass_sphere2": glass_sphere2,
     "hexagon": hexagon,
+    "solids_field": solids_field,
     "teapot_standin": teapot_standin,    # config 4
     "mesh_and_spheres": mesh_and_spheres,  # config 5
 }

@@ -8,6 +8,7 @@ SMALL_CASES = [
     ("primitives_csg", dict(width=160, height=90), 1),
     ("glass_sphere2", dict(width=80, height=80), 1),
     ("hexagon", dict(width=128, height=72), 1),
+    ("solids_field", dict(width=160, height=90), 1),
     ("reflect_refract", dict(width=64, height=36), 4),
     ("glass_sphere2", dict(width=32, height=32, aa=16), 16),
 ]
