@@ -103,20 +103,30 @@ RTC_HD bool own_box(double lx, double ly, double lz, double hx, double hy, doubl
   return tmin <= tmax + 1e-9 * (fabs(tmin) + fabs(tmax));
 }
 
-// Lazy division. t = num/den (den > 0) is only worth an IEEE division (≈ a dozen FP64-pipe
-// instructions) if the query could want it. These pre-filters never reject a t the query would
-// take: the sign of the quotient is the sign of num (magnitudes kept away from underflow, where
-// -tiny/den could round to -0.0, which `t >= 0.0` accepts), and num > limit·den·(1+1e-9) puts the
-// correctly rounded quotient strictly beyond the limit (the tie t == limit is never filtered).
+// Lazy division. t = num/den is only worth an IEEE division (≈ a dozen FP64-pipe instructions) if
+// the query could want it. These pre-filters never reject a t the query would take: the sign of the
+// quotient is the sign of num·den (magnitudes kept away from underflow, where -tiny/den could round
+// to -0.0, which `t >= 0.0` accepts), and |num| > limit·(1+1e-9)·|den| puts the correctly rounded
+// positive quotient strictly beyond the limit (the tie t == limit is never filtered). The range and
+// sign tests read the upper word of the doubles as integers — no 64-bit constants in the hot loops.
+// NaN and ±inf numerators are never filtered (a NaN t has to reach the caller's NaN check).
 RTC_HD bool quot_unwanted(const Query& C, double num, double den) {
-  if (!(den > 0.0) || !(den < 1e150)) return false;
 #if defined(RTK_QUERY_BRANCHY)
+  if (den < 0.0) { num = -num; den = -den; }
+  if (!(den > 0.0) || !(den < 1e150)) return false;
   if (C.mode == Q_NEG) return num > 1e-150;
   if (num < -1e-150) return true;
   return num > C.limit * den * (1.0 + 1e-9);
 #else
-  const double wrong_side = C.mode == Q_NEG ? -num : num;  // Q_NEG wants t < 0 (its limit is +inf)
-  return (wrong_side < -1e-150) | (num > C.limit * den * (1.0 + 1e-9));
+  const uint32_t dh = hi_word(den), nh = hi_word(num);
+  // |den| in [2^-1022, ~1e150): 0x00100000 <= upper word < 0x5F138D35 (upper word of 1e150)
+  const bool den_ok = ((dh & 0x7fffffffu) - 0x00100000u) < (0x5F138D35u - 0x00100000u);
+  const uint32_t qh = nh ^ (dh & 0x80000000u);                       // upper word of num carrying the quotient's sign
+  const uint32_t th = qh ^ (C.mode == Q_NEG ? 0x80000000u : 0u);     // Q_NEG wants t < 0: flip
+  // wrong side: sign set and 1e-150 < |num| < inf (upper word of 1e-150 is 0x20CA2FE7)
+  const bool wrong_side = (th - 0xA0CA2FE8u) < (0xFFF00000u - 0xA0CA2FE8u);
+  const bool beyond = ((qh >> 31) == 0u) & (fabs(num) > C.limit_hi * fabs(den));
+  return den_ok & (wrong_side | beyond);
 #endif
 }
 
@@ -185,8 +195,7 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
       const double oy = m4 * ray.o.x + m5 * ray.o.y + m6 * ray.o.z + m7;  // matrix.rs:240, row 1
       const double dy = m4 * ray.d.x + m5 * ray.d.y + m6 * ray.d.z;       // matrix.rs:255, row 1
       if (fabs(dy) < EPS) continue;
-      const bool neg = dy < 0.0;
-      if (quot_unwanted(C, neg ? oy : -oy, neg ? -dy : dy)) continue;
+      if (quot_unwanted(C, -oy, dy)) continue;
       cand(-oy / dy, i, flags, par);
     }
     // current item: a run of prims [first, first+count) (leaf) or a BVH node (cur >= 0)

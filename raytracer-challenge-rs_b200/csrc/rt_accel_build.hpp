@@ -311,7 +311,10 @@ struct Builder {
 
 }  // namespace accel_detail
 
-constexpr int BVH_MIN_PRIMS = 8;  // fewer BVH-eligible prims than this: test them all, no BVH
+#ifndef RTK_BVH_MIN_PRIMS
+#define RTK_BVH_MIN_PRIMS 8
+#endif
+constexpr int BVH_MIN_PRIMS = RTK_BVH_MIN_PRIMS;  // fewer BVH-eligible prims than this: test them all, no BVH
 
 inline void fill_recs(const rtc_scene_desc* d, AccelBuild& A) {
   // kind-sorted so the every-ray loop runs one tight, switch-free loop per common kind; the order

@@ -47,15 +47,18 @@ struct HitList {
 };
 
 struct Query {
-  double limit;      // Q_CLOSEST: best t so far (inf); Q_SHADOW: distance to the light
+  double limit;      // Q_CLOSEST: best t so far (inf); Q_SHADOW: distance to the light; Q_NEG: inf
+  double limit_hi;   // limit * (1 + 1e-9): what a not-yet-divided quotient is compared with (quot_unwanted)
   int32_t mode;
   int32_t node;      // Q_CLOSEST: best node (-1); Q_SHADOW: 1 when found
   HitList* list;     // Q_NEG
   uint32_t* err;
 
-  RTC_HD void init_closest(uint32_t* e) { mode = Q_CLOSEST; limit = rt_inf(); node = -1; list = nullptr; err = e; }
-  RTC_HD void init_shadow(double distance, uint32_t* e) { mode = Q_SHADOW; limit = distance; node = 0; list = nullptr; err = e; }
-  RTC_HD void init_neg(HitList* l, uint32_t* e) { mode = Q_NEG; limit = rt_inf(); node = -1; list = l; l->n = 0; err = e; }
+  RTC_HD void init_closest(uint32_t* e) { mode = Q_CLOSEST; limit = limit_hi = rt_inf(); node = -1; list = nullptr; err = e; }
+  RTC_HD void init_shadow(double distance, uint32_t* e) {
+    mode = Q_SHADOW; limit = distance; limit_hi = distance * (1.0 + 1e-9); node = 0; list = nullptr; err = e;
+  }
+  RTC_HD void init_neg(HitList* l, uint32_t* e) { mode = Q_NEG; limit = limit_hi = rt_inf(); node = -1; list = l; l->n = 0; err = e; }
 
   // would the reference's sorted list hand this intersection to the caller? One branch-free form for
   // the three modes (lanes of a warp are in different modes): the sign test flips for Q_NEG, whose
@@ -74,7 +77,7 @@ struct Query {
 #endif
   }
   RTC_HD void take(double t, int32_t nd) {
-    if (mode == Q_CLOSEST) { limit = t; node = nd; return; }
+    if (mode == Q_CLOSEST) { limit = t; limit_hi = t * (1.0 + 1e-9); node = nd; return; }
     if (mode == Q_SHADOW) { node = 1; return; }
     int n = list->n;
     if (n >= HIT_CAP) { *err |= ERR_OVERFLOW; return; }
