@@ -46,7 +46,7 @@ def nvcc_path():
 def build_cuda(force=False):
     csrc = os.path.join(HERE, "csrc")
     out = os.path.join(csrc, "librtc_cuda.so")
-    srcs = _glob(csrc, (".cu", ".cuh")) + [os.path.join(ROOT, "include", "rtc.h")]
+    srcs = _glob(csrc, (".cu", ".cuh", ".hpp")) + [os.path.join(ROOT, "include", "rtc.h")]
     if force or _newer(out, srcs):
         _run([nvcc_path()] + NVCC_FLAGS + ["-o", out, os.path.join(csrc, "rtc_api.cu")])
     return out
@@ -80,7 +80,7 @@ def build_oracle(force=False):
 def build_emul(force=False):
     d = os.path.join(ROOT, "tests", "cpu_emul")
     out = os.path.join(d, "libemul.so")
-    srcs = [os.path.join(d, "emul.cpp")] + _glob(os.path.join(HERE, "csrc"), (".cuh",)) + [os.path.join(ROOT, "include", "rtc.h")]
+    srcs = [os.path.join(d, "emul.cpp")] + _glob(os.path.join(HERE, "csrc"), (".cuh", ".hpp")) + [os.path.join(ROOT, "include", "rtc.h")]
     if force or _newer(out, srcs):
         # hidden visibility + -Bsymbolic: the inline rtk:: helpers it shares with librtc_cuda.so must not interpose
         _run(["g++"] + GXX_FLAGS + ["-fvisibility=hidden", "-Wl,-Bsymbolic", "-shared", "-o", out, os.path.join(d, "emul.cpp")])

@@ -161,11 +161,12 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
       RTK_COUNT(prim_tests, 1);
 #if defined(__CUDA_ARCH__)
       const int4 hd = __ldg(reinterpret_cast<const int4*>(rec));
-      const int32_t i = hd.x, par = hd.w;
+      const int32_t i = hd.x, par = hd.z;
+      const uint32_t flags = (uint32_t)hd.w & 0xffffffu;
 #else
       const int32_t i = rec->node, par = rec->parent;
+      const uint32_t flags = rec->kind_flags & 0xffffffu;
 #endif
-      const uint32_t flags = RTC_LDG(&rec->flags);
       const RayD r = ray_transform_v2(rec->inv, ray);
       const double a = dot(r.d, r.d);
       const double b = 2.0 * dot(r.d, r.o);
@@ -183,15 +184,16 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
       RTK_COUNT(prim_tests, 1);
 #if defined(__CUDA_ARCH__)
       const int4 hd = __ldg(reinterpret_cast<const int4*>(rec));
-      const int32_t i = hd.x, par = hd.w;
+      const int32_t i = hd.x, par = hd.z;
+      const uint32_t flags = (uint32_t)hd.w & 0xffffffu;
       const double2 m45 = __ldg(reinterpret_cast<const double2*>(rec->inv + 4));
       const double2 m67 = __ldg(reinterpret_cast<const double2*>(rec->inv + 6));
       const double m4 = m45.x, m5 = m45.y, m6 = m67.x, m7 = m67.y;
 #else
       const int32_t i = rec->node, par = rec->parent;
+      const uint32_t flags = rec->kind_flags & 0xffffffu;
       const double m4 = rec->inv[4], m5 = rec->inv[5], m6 = rec->inv[6], m7 = rec->inv[7];
 #endif
-      const uint32_t flags = RTC_LDG(&rec->flags);
       const double oy = m4 * ray.o.x + m5 * ray.o.y + m6 * ray.o.z + m7;  // matrix.rs:240, row 1
       const double dy = m4 * ray.d.x + m5 * ray.d.y + m6 * ray.d.z;       // matrix.rs:255, row 1
       if (fabs(dy) < EPS) continue;
@@ -213,11 +215,14 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
             const PrimRec* rec = S.recs + k;
 #if defined(__CUDA_ARCH__)
             const int4 hd = __ldg(reinterpret_cast<const int4*>(rec));
-            i = hd.x; nd.kind = hd.y; nd.aux = hd.z; par = hd.w;
+            i = hd.x; nd.aux = hd.y; par = hd.z;
+            const uint32_t kf = (uint32_t)hd.w;
 #else
-            i = rec->node; nd.kind = rec->kind; nd.aux = rec->aux; par = rec->parent;
+            i = rec->node; nd.aux = rec->aux; par = rec->parent;
+            const uint32_t kf = rec->kind_flags;
 #endif
-            nd.flags = RTC_LDG(&rec->flags);
+            nd.kind = (int32_t)(kf >> 24);
+            nd.flags = kf & 0xffffffu;
             if (nd.kind == RTC_CSG) {
               if constexpr (HAS_CSG) {
                 // the reference reaches this CSG only through its enclosing groups: validate first

@@ -38,9 +38,9 @@ struct BvhNode {     // 128 bytes: both children's boxes in one fetch
 };
 
 struct PrimRec {     // 128 bytes: everything the every-ray loop needs about one prim, in one place
-  int32_t node, kind, aux, parent;
-  uint32_t flags;
-  int32_t _pad[3];
+  int32_t node, aux, parent;
+  uint32_t kind_flags;   // kind << 24 | flags — the whole header is one 16-byte load
+  int32_t _pad[4];
   double inv[12];    // rows 0..2 of the leaf's transform_inverse (unused for a CSG prim)
 };
 
@@ -331,7 +331,8 @@ inline void fill_recs(const rtc_scene_desc* d, AccelBuild& A) {
     const int32_t i = A.prims[(size_t)k];
     const rtc_node& nd = d->nodes[i];
     PrimRec& r = A.recs[(size_t)k];
-    r.node = i; r.kind = nd.kind; r.aux = nd.aux; r.parent = A.parent[(size_t)i]; r.flags = nd.flags;
+    r.node = i; r.aux = nd.aux; r.parent = A.parent[(size_t)i];
+    r.kind_flags = ((uint32_t)nd.kind << 24) | (nd.flags & 0xffffffu);
     if (nd.kind != RTC_CSG)
       for (int c = 0; c < 12; c++) r.inv[c] = d->xforms[12 * (size_t)nd.xform + c];
   }

@@ -126,7 +126,7 @@ RTC_HD void prepare(const SceneView& S, const RayD& ray, double t, int32_t node,
   c.node = node;
   c.point = ray_position(ray, t);
   c.eyev = -ray.d;
-  const double* inv = S.xforms + 12 * (size_t)nd.xform;
+  const M34 inv = load_m34(S.xforms + 12 * (size_t)nd.xform);
   V3 local_point = xf_point(inv, c.point);                       // geometry/mod.rs:52
   V3 ln = local_normal(S, nd, local_point, node, ray);           // :53
   V3 n = normalize(xf_vector_transposed(inv, ln));               // :54-55
@@ -153,7 +153,7 @@ RTC_HD long long as_isize(double v) {  // Rust `as isize`: saturating, NaN → 0
 // Pattern::color_at_shape (pattern/mod.rs:39-49)
 RTC_HD V3 pattern_color(const SceneView& S, int32_t pat, const double* leaf_inv, V3 world_point) {
   const rtc_pattern* P = S.patterns + pat;
-  V3 op = xf_point(leaf_inv, world_point);
+  V3 op = xf_point(load_m34(leaf_inv), world_point);
   V3 p = xf_point(P->inverse, op);
   V3 a = v3(RTC_LDG(&P->a[0]), RTC_LDG(&P->a[1]), RTC_LDG(&P->a[2]));
   V3 b = v3(RTC_LDG(&P->b[0]), RTC_LDG(&P->b[1]), RTC_LDG(&P->b[2]));

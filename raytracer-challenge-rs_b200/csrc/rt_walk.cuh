@@ -24,7 +24,7 @@ constexpr int CSG_MAX_DEPTH = 4;    // nested CSG levels per ray
 constexpr int HIT_CAP = 64;         // bounded list capacity (CSG hit buffer, negative-t list)
 
 enum : uint32_t { ERR_OVERFLOW = 1u, ERR_NAN = 2u };
-enum : int32_t { Q_CLOSEST = 0, Q_SHADOW = 1, Q_NEG = 2 };
+enum : int32_t { Q_CLOSEST = 0, Q_SHADOW = 1, Q_NEG = 2, Q_DONE = 3 };  // Q_DONE: a Q_SHADOW that found its occluder
 
 RTC_HD rtc_node load_node(const rtc_node* p) {
 #if defined(__CUDA_ARCH__)
@@ -78,7 +78,7 @@ struct Query {
   }
   RTC_HD void take(double t, int32_t nd) {
     if (mode == Q_CLOSEST) { limit = t; limit_hi = t * (1.0 + 1e-9); node = nd; return; }
-    if (mode == Q_SHADOW) { node = 1; return; }
+    if (mode & 1) { node = 1; mode = Q_DONE; return; }  // Q_SHADOW, or Q_DONE again (further hits of the same leaf)
     int n = list->n;
     if (n >= HIT_CAP) { *err |= ERR_OVERFLOW; return; }
     int k = n;
@@ -93,7 +93,7 @@ struct Query {
     list->n = n + 1;
   }
   RTC_HD void hit(double t, int32_t nd, uint32_t flags) { if (want(t, nd, flags)) take(t, nd); }
-  RTC_HD bool done() const { return mode == Q_SHADOW && node != 0; }
+  RTC_HD bool done() const { return mode == Q_DONE; }
   // conservative t-range culling of one of OUR boxes [tmin,tmax] (never of a reference box)
   RTC_HD bool cull(double tmin, double tmax) const {
     if (mode == Q_NEG) return tmin > 1e-6 * (1.0 + fabs(tmin));
