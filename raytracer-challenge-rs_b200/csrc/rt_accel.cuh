@@ -156,9 +156,8 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
     };
     // ---- every-ray spheres (sphere.rs:47-62): switch-free, divisions only for wanted roots ---------
     int32_t k0 = 0;
-    for (; k0 < S.n_sph && !C.done(); k0++) {
-      const PrimRec* rec = S.recs + k0;
-      RTK_COUNT(prim_tests, 1);
+    // the roots of one sphere whose discriminant is not negative
+    auto sphere_roots = [&](const PrimRec* rec, double a, double b, double disc) {
 #if defined(__CUDA_ARCH__)
       const int4 hd = __ldg(reinterpret_cast<const int4*>(rec));
       const int32_t i = hd.x, par = hd.z;
@@ -167,16 +166,25 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
       const int32_t i = rec->node, par = rec->parent;
       const uint32_t flags = rec->kind_flags & 0xffffffu;
 #endif
-      const RayD r = ray_transform_v2(rec->inv, ray);
-      const double a = dot(r.d, r.d);
-      const double b = 2.0 * dot(r.d, r.o);
-      const double c = dot(r.o, r.o) - 1.0;
-      const double disc = b * b - 4.0 * a * c;
-      if (disc < 0.0) continue;
       const double sq = sqrt(disc);
       const double a2 = 2.0 * a, num1 = -b - sq, num2 = -b + sq;
       if (!quot_unwanted(C, num1, a2)) cand(num1 / a2, i, flags, par);
       if (!quot_unwanted(C, num2, a2)) cand(num2 / a2, i, flags, par);
+    };
+    auto sphere_disc = [&](const PrimRec* rec, double& a, double& b) {
+      const RayD r = ray_transform_v2(rec->inv, ray);
+      a = dot(r.d, r.d);
+      b = 2.0 * dot(r.d, r.o);
+      const double c = dot(r.o, r.o) - 1.0;
+      return b * b - 4.0 * a * c;
+    };
+    for (; k0 < S.n_sph && !C.done(); k0++) {
+      const PrimRec* rec = S.recs + k0;
+      RTK_COUNT(prim_tests, 1);
+      double a, b;
+      const double disc = sphere_disc(rec, a, b);
+      if (disc < 0.0) continue;
+      sphere_roots(rec, a, b, disc);
     }
     // ---- every-ray planes (plane.rs:53-60): only row 1 of the inverse is needed --------------------
     for (; k0 < S.n_sph + S.n_pl && !C.done(); k0++) {
