@@ -208,92 +208,105 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
       if (quot_unwanted(C, -oy, dy)) continue;
       cand(-oy / dy, i, flags, par);
     }
-    // current item: a run of prims [first, first+count) (leaf) or a BVH node (cur >= 0)
-    int32_t first = k0, count = S.n_always - k0, cur = -1;
+    // ---- the remaining every-ray prims, then the BVH ---------------------------------------------------
+    // "while-while" traversal: every lane first walks inner nodes until it holds a leaf (or runs out),
+    // and only then does the warp test leaf prims — so the (long) leaf code runs with as many lanes as
+    // have a leaf, instead of interleaving with other lanes' node tests. Items: a run of prims
+    // [first, first+count) or a BVH node `cur`; refs on the stack are >= 0 for inner nodes and
+    // ~(first << 3 | count) for leaves.
+    constexpr int32_t NONE = -0x7fffffff - 1;
+    int32_t first = k0, count = S.n_always - k0, cur = NONE;
     if (C.done()) return;
     for (;;) {
-      if (cur < 0) {
-        for (int32_t k = first; k < first + count && !C.done(); k++) {
-          int32_t i, par;
-          rtc_node nd;
-          LeafHits hits;
-          bool generic = false;
-          RTK_COUNT(prim_tests, 1);
-          if (k < S.n_always) {  // (uniform per run) every-ray prim: one 128-byte record
-            const PrimRec* rec = S.recs + k;
+      // -- leaf phase
+      for (int32_t k = first; k < first + count && !C.done(); k++) {
+        int32_t i, par;
+        rtc_node nd;
+        LeafHits hits;
+        bool generic = false;
+        RTK_COUNT(prim_tests, 1);
+        if (k < S.n_always) {  // (uniform per run) every-ray prim: one 128-byte record
+          const PrimRec* rec = S.recs + k;
 #if defined(__CUDA_ARCH__)
-            const int4 hd = __ldg(reinterpret_cast<const int4*>(rec));
-            i = hd.x; nd.aux = hd.y; par = hd.z;
-            const uint32_t kf = (uint32_t)hd.w;
+          const int4 hd = __ldg(reinterpret_cast<const int4*>(rec));
+          i = hd.x; nd.aux = hd.y; par = hd.z;
+          const uint32_t kf = (uint32_t)hd.w;
 #else
-            i = rec->node; nd.aux = rec->aux; par = rec->parent;
-            const uint32_t kf = rec->kind_flags;
+          i = rec->node; nd.aux = rec->aux; par = rec->parent;
+          const uint32_t kf = rec->kind_flags;
 #endif
-            nd.kind = (int32_t)(kf >> 24);
-            nd.flags = kf & 0xffffffu;
-            if (nd.kind == RTC_CSG) {
-              if constexpr (HAS_CSG) {
-                // the reference reaches this CSG only through its enclosing groups: validate first
-                if (chain_ok(S, par, ray, ok_group)) walk_range<true>(S, ray, C, cs, err, i, RTC_LDG(&S.nodes[i].skip));
-              }
-              continue;
+          nd.kind = (int32_t)(kf >> 24);
+          nd.flags = kf & 0xffffffu;
+          if (nd.kind == RTC_CSG) {
+            if constexpr (HAS_CSG) {
+              // the reference reaches this CSG only through its enclosing groups: validate first
+              if (chain_ok(S, par, ray, ok_group)) walk_range<true>(S, ray, C, cs, err, i, RTC_LDG(&S.nodes[i].skip));
             }
-            lr = ray_transform_v2(rec->inv, ray);
-            lr_xf = -1;
+            continue;
+          }
+          lr = ray_transform_v2(rec->inv, ray);
+          lr_xf = -1;
+          generic = true;
+        } else {  // BVH prim: one 96-byte record, geometry inline (no node → triangle indirection)
+          const LeafRec* lrec = S.leaf_recs + (k - S.n_always);
+#if defined(__CUDA_ARCH__)
+          const int4 hd = __ldg(reinterpret_cast<const int4*>(lrec));
+          i = hd.x; par = hd.z;
+          const int32_t xf = hd.y;
+          const uint32_t kf = (uint32_t)hd.w;
+#else
+          i = lrec->node; par = lrec->parent;
+          const int32_t xf = lrec->xform;
+          const uint32_t kf = lrec->kind_flags;
+#endif
+          nd.kind = (int32_t)(kf >> 24);
+          nd.flags = kf & 0xffffffu;
+          if (xf != lr_xf) {
+            lr = ray_transform(S.xforms + 12 * (size_t)xf, ray);
+            lr_xf = xf;
+          }
+          hits.n = 0;
+          hits.t0 = hits.t1 = hits.t2 = hits.t3 = 0.0;
+          if (nd.kind == RTC_SPHERE) {
+            isect_sphere(lr, [&](double t) { hits.push(t); });
+          } else if (nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE) {
+            double t, u, v;
+            if (isect_triangle(lr, lrec->g, t, u, v)) hits.push(t);
+          } else {  // cube, bounded cylinder
+            nd.aux = RTC_LDG(&lrec->aux);
             generic = true;
-          } else {  // BVH prim: one 96-byte record, geometry inline (no node → triangle indirection)
-            const LeafRec* lrec = S.leaf_recs + (k - S.n_always);
-#if defined(__CUDA_ARCH__)
-            const int4 hd = __ldg(reinterpret_cast<const int4*>(lrec));
-            i = hd.x; par = hd.z;
-            const int32_t xf = hd.y;
-            const uint32_t kf = (uint32_t)hd.w;
-#else
-            i = lrec->node; par = lrec->parent;
-            const int32_t xf = lrec->xform;
-            const uint32_t kf = lrec->kind_flags;
-#endif
-            nd.kind = (int32_t)(kf >> 24);
-            nd.flags = kf & 0xffffffu;
-            if (xf != lr_xf) {
-              lr = ray_transform(S.xforms + 12 * (size_t)xf, ray);
-              lr_xf = xf;
-            }
-            hits.n = 0;
-            hits.t0 = hits.t1 = hits.t2 = hits.t3 = 0.0;
-            if (nd.kind == RTC_SPHERE) {
-              isect_sphere(lr, [&](double t) { hits.push(t); });
-            } else if (nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE) {
-              double t, u, v;
-              if (isect_triangle(lr, lrec->g, t, u, v)) hits.push(t);
-            } else {  // cube, bounded cylinder
-              nd.aux = RTC_LDG(&lrec->aux);
-              generic = true;
-            }
           }
-          if (generic) {  // ONE isect_leaf site for every-ray prims and the BVH's non-triangle kinds
-            LeafHits h;
-            isect_leaf(S, nd, lr, h);
-            hits = h;
-          }
-          const LeafHits& h = hits;
+        }
+        if (generic) {  // ONE isect_leaf site for every-ray prims and the BVH's non-triangle kinds
+          LeafHits h;
+          isect_leaf(S, nd, lr, h);
+          hits = h;
+        }
+        const LeafHits& h = hits;
 #if defined(__CUDACC__)
 #pragma unroll 1
 #endif
-          for (int j = 0; j < h.n; j++) {
-            const double t = j == 0 ? h.t0 : (j == 1 ? h.t1 : (j == 2 ? h.t2 : h.t3));
-            cand(t, i, nd.flags, par);
-          }
+        for (int j = 0; j < h.n; j++) {
+          const double t = j == 0 ? h.t0 : (j == 1 ? h.t1 : (j == 2 ? h.t2 : h.t3));
+          cand(t, i, nd.flags, par);
         }
-        if (C.done() || S.n_bvh <= 0) return;
-        if (!have_inv) {  // the always-run is done: enter the BVH at its root
-          inv = v3(1.0 / ray.d.x, 1.0 / ray.d.y, 1.0 / ray.d.z);
-          plain = ray.d.x != 0.0 && ray.d.y != 0.0 && ray.d.z != 0.0 && ray.d.x == ray.d.x && ray.d.y == ray.d.y && ray.d.z == ray.d.z;
-          have_inv = true;
-          cur = 0;
-          continue;
-        }
+      }
+      if (C.done() || S.n_bvh <= 0) return;
+      if (!have_inv) {  // the always-run is done: enter the BVH at its root
+        inv = v3(1.0 / ray.d.x, 1.0 / ray.d.y, 1.0 / ray.d.z);
+        plain = ray.d.x != 0.0 && ray.d.y != 0.0 && ray.d.z != 0.0 && ray.d.x == ray.d.x && ray.d.y == ray.d.y && ray.d.z == ray.d.z;
+        have_inv = true;
+        cur = 0;
       } else {
+        cur = NONE;
+        while (sp > 0) {
+          sp--;
+          if (!C.cull(st->tmin[sp], rt_inf())) { cur = st->node[sp]; break; }
+        }
+        if (cur == NONE) return;
+      }
+      // -- node phase: descend until this lane holds a leaf ref (cur < 0) or nothing (NONE)
+      while (cur >= 0) {
         const BvhNode* bn = S.bvh + cur;
         RTK_COUNT(bvh_nodes, 1);
 #if defined(__CUDA_ARCH__)
@@ -315,8 +328,7 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
         // refs: >= 0 inner node, < 0 leaf ~(first << 3 | count)
         const int32_t r0 = n0 > 0 ? ~((c0 << 3) | n0) : c0;
         const int32_t r1 = n1 > 0 ? ~((c1 << 3) | n1) : c1;
-        cur = -1;
-        count = 0;
+        cur = NONE;
         if (h0 && h1) {
           const bool swap = t1min < t0min;  // near child first, far child on the stack with its tmin
           if (sp < BVH_STACK) {
@@ -329,28 +341,18 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
           cur = swap ? r1 : r0;
         } else if (h0 || h1) {
           cur = h0 ? r0 : r1;
-        }
-        if (cur >= 0) continue;           // descend into an inner node
-        if (h0 || h1) {                   // a leaf: decode and test it next iteration
-          const int32_t ref = ~cur;
-          first = ref >> 3;
-          count = ref & 7;
-          cur = -1;
-          continue;
+        } else {
+          while (sp > 0) {
+            sp--;
+            if (!C.cull(st->tmin[sp], rt_inf())) { cur = st->node[sp]; break; }
+          }
         }
       }
-      // pop
-      bool got = false;
-      while (sp > 0) {
-        sp--;
-        if (!C.cull(st->tmin[sp], rt_inf())) { cur = st->node[sp]; got = true; break; }
-      }
-      if (!got) return;
-      if (cur < 0) {
+      if (cur == NONE) return;
+      {
         const int32_t ref = ~cur;
         first = ref >> 3;
         count = ref & 7;
-        cur = -1;
       }
     }
   }
