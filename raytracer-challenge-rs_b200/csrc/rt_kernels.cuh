@@ -50,8 +50,12 @@ __device__ __forceinline__ void flush_counters(const RayCounters& rc, uint32_t e
 // so the lanes of a warp put near-identical queries to the scene and stay in the same phase of the
 // Tracer state machine. (A persistent variant with lane-level re-fill was measured and rejected:
 // profiles/r01b_experiment_persistent_refill.md.)
-template <bool HAS_CSG, bool FAITHFUL>
-__global__ void __launch_bounds__(128, RTK_MIN_BLOCKS) render_kernel(SceneView S, CameraD cam, RenderParams P, double* __restrict__ out,
+// MINB = CTAs per SM the register budget is cut for: 4 (128 registers; the FP64 state of search and
+// shading just fits) for scenes whose tables live in L1/L2; 8 (64 registers, 32 warps per SM) for BVHs
+// far larger than L2, where traversal waits on DRAM and only more warps hide it (1 M triangles at 4K:
+// 91 → 69 ms; an 8 k-triangle mesh is 25 % slower that way, so the host picks by accelerator size).
+template <bool HAS_CSG, bool FAITHFUL, int MINB = RTK_MIN_BLOCKS>
+__global__ void __launch_bounds__(128, MINB) render_kernel(SceneView S, CameraD cam, RenderParams P, double* __restrict__ out,
                                                                      unsigned long long* __restrict__ counters) {
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   const uint32_t px = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);

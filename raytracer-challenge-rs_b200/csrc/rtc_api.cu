@@ -39,6 +39,7 @@ struct rtc_scene {
   size_t slab_bytes = 0;
   SceneView view{};
   bool has_csg = false;
+  bool big_accel = false;  // BVH + leaf records well beyond L2: launch the 32-warps-per-SM kernel
   unsigned long long* d_counters = nullptr;
   double* d_canvas = nullptr;  // cached device canvas for rtc_render
   size_t canvas_doubles = 0;
@@ -179,9 +180,11 @@ int launch_rows(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool fa
   if (grid.x > 0 && grid.y > 0) {
     if (s->has_csg) {
       if (faithful) render_kernel<true, true><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
+      else if (s->big_accel) render_kernel<true, false, 8><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
       else render_kernel<true, false><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
     } else {
       if (faithful) render_kernel<false, true><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
+      else if (s->big_accel) render_kernel<false, false, 8><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
       else render_kernel<false, false><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
     }
     s->launches++;
@@ -281,6 +284,8 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   rtc_scene* s = new rtc_scene();
   s->device = device;
   s->has_csg = has_csg;
+  // 126 MB of L2 on B200: past ~64 MB of nodes + leaf records, traversal is DRAM-latency bound
+  s->big_accel = sizeof(BvhNode) * accel.bvh.size() + sizeof(LeafRec) * accel.leaf_recs.size() > ((size_t)64 << 20);
   s->slab_bytes = total;
   auto bail = [&](cudaError_t e, const char* what) {
     std::string m = std::string(what) + ": " + cudaGetErrorString(e);
