@@ -22,7 +22,12 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
+#include <atomic>
+#include <chrono>
+#include <cstdio>
 #include <limits>
+#include <thread>
 #include <vector>
 
 #include "../../include/rtc.h"
@@ -111,9 +116,22 @@ inline void xf(const double* m, const double p[3], double out[3]) {
 }
 
 // Our own world-space bound of a BVH-eligible leaf (triangle, smooth triangle, sphere).
-inline bool leaf_world_box(const rtc_scene_desc* d, const rtc_node& nd, Box& out) {
-  double fwd[12];
-  if (!invert_affine(d->xforms + 12 * (size_t)nd.xform, fwd)) return false;
+// Forward matrices of the scene's (de-duplicated) inverse transforms, inverted on first use: a mesh's
+// million triangles share one.
+struct FwdCache {
+  std::vector<double> m;
+  std::vector<signed char> state;  // 0 unknown, 1 ok, -1 singular
+  explicit FwdCache(size_t n_xforms) : m(12 * n_xforms), state(n_xforms, 0) {}
+  const double* get(const rtc_scene_desc* d, int32_t xf) {
+    signed char& st = state[(size_t)xf];
+    if (st == 0) st = invert_affine(d->xforms + 12 * (size_t)xf, &m[12 * (size_t)xf]) ? 1 : -1;
+    return st > 0 ? &m[12 * (size_t)xf] : nullptr;
+  }
+};
+
+inline bool leaf_world_box(const rtc_scene_desc* d, const rtc_node& nd, Box& out, FwdCache& cache) {
+  const double* fwd = cache.get(d, nd.xform);
+  if (!fwd) return false;
   out.reset();
   double w[3];
   if (nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE) {
@@ -168,10 +186,32 @@ struct Builder {
   std::vector<Prim>& prims;
   AccelBuild& out;
   const rtc_scene_desc* desc;
-  explicit Builder(std::vector<Prim>& p, AccelBuild& o, const rtc_scene_desc* d) : prims(p), out(o), desc(d) {}
+  int threads = 1;                         // worker threads for large ranges / independent subtrees
+  int PAR_MIN = 1 << 16;                   // ranges below this are binned on the calling thread
+  explicit Builder(std::vector<Prim>& p, AccelBuild& o, const rtc_scene_desc* d) : prims(p), out(o), desc(d) {
+    unsigned hc = std::thread::hardware_concurrency();
+    threads = hc == 0 ? 1 : (hc > 16 ? 16 : (int)hc);
+    if (const char* v = std::getenv("RTC_BVH_THREADS")) threads = std::max(1, std::min(64, std::atoi(v)));
+    if (const char* v = std::getenv("RTC_BVH_PAR_MIN")) {  // tests: push small meshes through the threaded path
+      PAR_MIN = std::max(8, std::atoi(v));
+      if (threads < 4) threads = 4;
+    }
+  }
+
+  // fn(chunk index, begin, end) over [b, e) cut into nchunk pieces; piece 0 runs on the caller
+  template <class F>
+  static void parallel_chunks(int b, int e, int nchunk, F&& fn) {
+    if (nchunk <= 1) { fn(0, b, e); return; }
+    std::vector<std::thread> pool;
+    const long long n = e - b;
+    for (int ci = 1; ci < nchunk; ci++)
+      pool.emplace_back([&, ci] { fn(ci, b + (int)(n * ci / nchunk), b + (int)(n * (ci + 1) / nchunk)); });
+    fn(0, b, b + (int)(n / nchunk));
+    for (auto& t : pool) t.join();
+  }
 
   // Split prims[b,e) — returns mid (b < mid < e), or -1 to make a leaf.
-  int split(int b, int e, const Box& bounds, int depth) {
+  int split(int b, int e, const Box& bounds, int depth, int nthreads) {
     const int n = e - b;
     if (n <= LEAF_MAX) return -1;
     if (depth >= 40) {  // bound the traversal stack: median split along the widest axis from here on
@@ -182,24 +222,59 @@ struct Builder {
                        [a](const Prim& x, const Prim& y) { return x.c[a] < y.c[a]; });
       return b + n / 2;
     }
+    // centroid bounds, then ONE pass that bins all three axes; both passes are cut into chunks run on
+    // worker threads when the range is large (the top levels of a million-triangle mesh)
+    const int nchunk = (n >= PAR_MIN && nthreads > 1) ? nthreads : 1;
+    std::vector<Box> cbs((size_t)nchunk);
+    parallel_chunks(b, e, nchunk, [&](int ci, int cb0, int ce0) {
+      Box x;
+      x.reset();
+      for (int k = cb0; k < ce0; k++) x.add(prims[(size_t)k].c);
+      cbs[(size_t)ci] = x;
+    });
     Box cb;
     cb.reset();
-    for (int k = b; k < e; k++) cb.add(prims[(size_t)k].c);
+    for (const Box& x : cbs) cb.add(x);
+    struct Bins {
+      Box bb[3][SAH_BINS];
+      int cnt[3][SAH_BINS];
+    };
+    double scale3[3];
+    bool use_axis[3];
+    for (int a = 0; a < 3; a++) {
+      const double ext = cb.hi[a] - cb.lo[a];
+      use_axis[a] = ext > 0.0;
+      scale3[a] = use_axis[a] ? SAH_BINS / ext : 0.0;
+    }
+    std::vector<Bins> part((size_t)nchunk);
+    parallel_chunks(b, e, nchunk, [&](int ci, int cb0, int ce0) {
+      Bins& B = part[(size_t)ci];
+      for (int a = 0; a < 3; a++)
+        for (int k = 0; k < SAH_BINS; k++) { B.bb[a][k].reset(); B.cnt[a][k] = 0; }
+      for (int k = cb0; k < ce0; k++) {
+        const Prim& p = prims[(size_t)k];
+        for (int a = 0; a < 3; a++) {
+          if (!use_axis[a]) continue;
+          int bi = (int)((p.c[a] - cb.lo[a]) * scale3[a]);
+          bi = bi < 0 ? 0 : (bi >= SAH_BINS ? SAH_BINS - 1 : bi);
+          B.bb[a][bi].add(p.box);
+          B.cnt[a][bi]++;
+        }
+      }
+    });
+    for (int ci = 1; ci < nchunk; ci++)
+      for (int a = 0; a < 3; a++)
+        for (int k = 0; k < SAH_BINS; k++)
+          if (part[(size_t)ci].cnt[a][k]) {
+            part[0].bb[a][k].add(part[(size_t)ci].bb[a][k]);
+            part[0].cnt[a][k] += part[(size_t)ci].cnt[a][k];
+          }
     int best_axis = -1, best_bin = -1;
     double best_cost = std::numeric_limits<double>::infinity();
     for (int a = 0; a < 3; a++) {
-      const double ext = cb.hi[a] - cb.lo[a];
-      if (!(ext > 0.0)) continue;
-      Box bb[SAH_BINS];
-      int cnt[SAH_BINS] = {0};
-      for (auto& x : bb) x.reset();
-      const double scale = SAH_BINS / ext;
-      for (int k = b; k < e; k++) {
-        int bi = (int)((prims[(size_t)k].c[a] - cb.lo[a]) * scale);
-        bi = bi < 0 ? 0 : (bi >= SAH_BINS ? SAH_BINS - 1 : bi);
-        bb[bi].add(prims[(size_t)k].box);
-        cnt[bi]++;
-      }
+      if (!use_axis[a]) continue;
+      const Box* bb = part[0].bb[a];
+      const int* cnt = part[0].cnt[a];
       double right_area[SAH_BINS];
       int right_cnt[SAH_BINS];
       Box acc;
@@ -254,12 +329,53 @@ struct Builder {
     if (which) { nd.c1 = c; nd.n1 = n; } else { nd.c0 = c; nd.n0 = n; }
   }
 
+  struct Task { int b, e, node, which, depth; };
+
+  // Build the subtrees on `stack` into `nodes`. With `deferred`, a range of fewer than defer_below prims
+  // is not built but handed back (its parent slot stays empty until the caller splices the subtree in).
+  void run(std::vector<BvhNode>& nodes, std::vector<Task>& stack, int defer_below, std::vector<Task>* deferred,
+           int32_t& max_depth, int nthreads) {
+    Box empty;
+    empty.reset();
+    while (!stack.empty()) {
+      Task t = stack.back();
+      stack.pop_back();
+      if (deferred && t.e - t.b < defer_below) {
+        deferred->push_back(t);
+        continue;
+      }
+      max_depth = std::max(max_depth, (int32_t)t.depth);
+      Box bx;
+      if (t.e - t.b >= PAR_MIN && nthreads > 1) {
+        std::vector<Box> parts((size_t)nthreads);
+        parallel_chunks(t.b, t.e, nthreads, [&](int ci, int b0, int e0) { parts[(size_t)ci] = range_box(prims, b0, e0); });
+        bx.reset();
+        for (const Box& x : parts) bx.add(x);
+      } else {
+        bx = range_box(prims, t.b, t.e);
+      }
+      int mid = split(t.b, t.e, bx, t.depth, nthreads);
+      if (mid < 0) {
+        std::sort(prims.begin() + t.b, prims.begin() + t.e, [](const Prim& x, const Prim& y) { return x.node < y.node; });
+        set_child(nodes[(size_t)t.node], t.which, bx, t.b, t.e - t.b);
+      } else {
+        int32_t id = (int32_t)nodes.size();
+        BvhNode nd{};
+        set_child(nd, 0, empty, 0, -1);
+        set_child(nd, 1, empty, 0, -1);
+        nodes.push_back(nd);
+        set_child(nodes[(size_t)t.node], t.which, bx, id, 0);
+        stack.push_back({t.b, mid, id, 0, t.depth + 1});
+        stack.push_back({mid, t.e, id, 1, t.depth + 1});
+      }
+    }
+  }
+
   void build() {
     const int n = (int)prims.size();
     out.bvh.clear();
     out.max_depth = 0;
     if (n == 0) return;
-    struct Task { int b, e, node, which, depth; };
     std::vector<Task> stack;
     BvhNode root{};
     Box empty;
@@ -268,24 +384,54 @@ struct Builder {
     set_child(root, 1, empty, 0, -1);
     out.bvh.push_back(root);
     stack.push_back({0, n, 0, 0, 1});
-    while (!stack.empty()) {
-      Task t = stack.back();
-      stack.pop_back();
-      out.max_depth = std::max(out.max_depth, (int32_t)t.depth);
-      Box bx = range_box(prims, t.b, t.e);
-      int mid = split(t.b, t.e, bx, t.depth);
-      if (mid < 0) {
-        std::sort(prims.begin() + t.b, prims.begin() + t.e, [](const Prim& x, const Prim& y) { return x.node < y.node; });
-        set_child(out.bvh[(size_t)t.node], t.which, bx, t.b, t.e - t.b);
-      } else {
-        int32_t id = (int32_t)out.bvh.size();
-        BvhNode nd{};
-        set_child(nd, 0, empty, 0, -1);
-        set_child(nd, 1, empty, 0, -1);
-        out.bvh.push_back(nd);
-        set_child(out.bvh[(size_t)t.node], t.which, bx, id, 0);
-        stack.push_back({t.b, mid, id, 0, t.depth + 1});
-        stack.push_back({mid, t.e, id, 1, t.depth + 1});
+    if (n < 4 * PAR_MIN || threads <= 1) {
+      run(out.bvh, stack, 0, nullptr, out.max_depth, 1);
+    } else {
+      // top of the tree on this thread (its big ranges binned by all threads), every subtree below
+      // n / (4·threads) prims built by a worker into its own node vector and spliced in afterwards in
+      // task order, so the tree does not depend on thread timing
+      std::vector<Task> deferred;
+      run(out.bvh, stack, std::max(n / (4 * threads), std::min(4096, PAR_MIN)), &deferred, out.max_depth, threads);
+      struct Sub { std::vector<BvhNode> nodes; int32_t depth = 0; };
+      std::vector<Sub> subs(deferred.size());
+      std::vector<size_t> order(deferred.size());
+      for (size_t i = 0; i < order.size(); i++) order[i] = i;
+      std::sort(order.begin(), order.end(), [&](size_t x, size_t y) { return deferred[x].e - deferred[x].b > deferred[y].e - deferred[y].b; });
+      std::atomic<size_t> next{0};
+      auto worker = [&]() {
+        for (;;) {
+          const size_t k = next.fetch_add(1);
+          if (k >= order.size()) return;
+          const size_t i = order[k];
+          Sub& sb = subs[i];
+          BvhNode holder{};
+          set_child(holder, 0, empty, 0, -1);
+          set_child(holder, 1, empty, 0, -1);
+          sb.nodes.push_back(holder);
+          std::vector<Task> st;
+          st.push_back({deferred[i].b, deferred[i].e, 0, 0, deferred[i].depth});
+          run(sb.nodes, st, 0, nullptr, sb.depth, 1);
+        }
+      };
+      std::vector<std::thread> pool;
+      for (int t = 1; t < threads; t++) pool.emplace_back(worker);
+      worker();
+      for (auto& t : pool) t.join();
+      for (size_t i = 0; i < deferred.size(); i++) {
+        const Sub& sb = subs[i];
+        const int32_t base = (int32_t)out.bvh.size() - 1;  // local node j (>= 1) becomes base + j
+        for (size_t j = 1; j < sb.nodes.size(); j++) {
+          BvhNode nd = sb.nodes[j];
+          if (nd.n0 == 0) nd.c0 += base;
+          if (nd.n1 == 0) nd.c1 += base;
+          out.bvh.push_back(nd);
+        }
+        const BvhNode& h = sb.nodes[0];
+        BvhNode& parent = out.bvh[(size_t)deferred[i].node];
+        Box bx;
+        for (int a = 0; a < 3; a++) { bx.lo[a] = h.lo0[a]; bx.hi[a] = h.hi0[a]; }
+        set_child(parent, deferred[i].which, bx, h.n0 == 0 ? h.c0 + base : h.c0, h.n0);
+        out.max_depth = std::max(out.max_depth, sb.depth);
       }
     }
     // BVH leaves address the combined prim array: shift by the always-prefix
@@ -341,6 +487,7 @@ inline void fill_recs(const rtc_scene_desc* d, AccelBuild& A) {
 // `d` must already be structurally valid (rtc_api.cu validate()).
 inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
   using namespace accel_detail;
+  const auto t0 = std::chrono::steady_clock::now();
   const int32_t n = (int32_t)d->n_nodes;
   A.parent.assign((size_t)n, -1);
   A.prims.clear();
@@ -348,6 +495,7 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
   A.bvh.clear();
   A.leaf_recs.clear();
   std::vector<Prim> cand;
+  FwdCache fwd_cache(d->n_xforms);
   struct Open { int32_t end, node; };
   std::vector<Open> groups;
   int32_t i = 0;
@@ -364,7 +512,7 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
     } else {
       Prim p;
       p.node = i;
-      if (nd.kind != RTC_PLANE && leaf_world_box(d, nd, p.box)) {
+      if (nd.kind != RTC_PLANE && leaf_world_box(d, nd, p.box, fwd_cache)) {
         for (int a = 0; a < 3; a++) p.c[a] = 0.5 * (p.box.lo[a] + p.box.hi[a]);
         cand.push_back(p);
       } else {
@@ -406,8 +554,15 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
   }
   A.n_always = (int32_t)A.prims.size();
   fill_recs(d, A);
+  const auto t1 = std::chrono::steady_clock::now();
   Builder b(cand, A, d);
   b.build();
+  if (std::getenv("RTC_TIMING")) {
+    const auto t2 = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "build_accel: walk+boxes+parents %.1f ms, BVH over %zu prims %.1f ms (%d threads)\n",
+                 std::chrono::duration<double, std::milli>(t1 - t0).count(), cand.size(),
+                 std::chrono::duration<double, std::milli>(t2 - t1).count(), b.threads);
+  }
 }
 
 }  // namespace rtk

@@ -4,6 +4,8 @@
 // No CPU fallback: every compute entry point needs a CUDA device.
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
+#include <cstdio>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -248,13 +250,16 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   *out = nullptr;
   std::vector<int32_t> csg_parent;
   bool has_csg = false;
+  const auto t_begin = std::chrono::steady_clock::now();
   int rc = validate(d, csg_parent, has_csg);
   if (rc) return rc;
+  const auto t_valid = std::chrono::steady_clock::now();
   if (rtc_device_count() <= device || device < 0) return fail(RTC_ERR_CUDA, "no such CUDA device (this library has no CPU fallback)");
   CUDA_TRY(cudaSetDevice(device));
 
   AccelBuild accel;
   build_accel(d, accel);
+  const auto t_accel = std::chrono::steady_clock::now();
   // one slab: [nodes | xforms | boxes | limits | tri_geom | tri_normals | materials | patterns | lights | csg_parent
   //            | parent | prims | bvh | recs | leaf_recs]
   struct Part { const void* src; size_t bytes; size_t off; };
@@ -316,12 +321,29 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   s->d_probe = (double*)(s->slab + total + align_up(N_COUNTERS * sizeof(unsigned long long)));
   if ((e = cudaEventCreate(&s->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
   if ((e = cudaEventCreate(&s->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
-  // stage on the host, one H2D copy
-  std::vector<char> stage(total, 0);
-  for (auto& p : parts)
-    if (p.bytes) std::memcpy(stage.data() + p.off, p.src, p.bytes);
-  if ((e = cudaMemcpyAsync(s->slab, stage.data(), total, cudaMemcpyHostToDevice, s->stream)) != cudaSuccess) return bail(e, "cudaMemcpy(scene)");
-  if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return bail(e, "cudaStreamSynchronize");
+  const auto t_built = std::chrono::steady_clock::now();
+  if (total <= ((size_t)1 << 20)) {
+    // small scene: stage on the host, one H2D copy (15 separate copies would cost more than the bytes)
+    std::vector<char> stage(total, 0);
+    for (auto& p : parts)
+      if (p.bytes) std::memcpy(stage.data() + p.off, p.src, p.bytes);
+    if ((e = cudaMemcpyAsync(s->slab, stage.data(), total, cudaMemcpyHostToDevice, s->stream)) != cudaSuccess) return bail(e, "cudaMemcpy(scene)");
+    if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return bail(e, "cudaStreamSynchronize");
+  } else {
+    // large scene (meshes): each table straight from where it lies, no host-side gather of hundreds of MB
+    for (auto& p : parts)
+      if (p.bytes && (e = cudaMemcpyAsync(s->slab + p.off, p.src, p.bytes, cudaMemcpyHostToDevice, s->stream)) != cudaSuccess)
+        return bail(e, "cudaMemcpy(scene table)");
+    if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return bail(e, "cudaStreamSynchronize");
+  }
+  if (std::getenv("RTC_TIMING")) {
+    auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+      return std::chrono::duration<double, std::milli>(b - a).count();
+    };
+    std::fprintf(stderr, "rtc_scene_create: validate %.2f ms, build_accel %.2f ms, alloc %.2f ms, upload %.2f ms (%.1f MB)\n",
+                 ms(t_begin, t_valid), ms(t_valid, t_accel), ms(t_accel, t_built), ms(t_built, std::chrono::steady_clock::now()),
+                 total / 1048576.0);
+  }
   SceneView& v = s->view;
   v.nodes = (const rtc_node*)(s->slab + parts[0].off);
   v.xforms = (const double*)(s->slab + parts[1].off);

@@ -10,6 +10,7 @@
 // kind-specific fields. Shapes that are equal only within the reference's 1e-5 epsilon but not
 // bit-equal get distinct classes (documented deviation).
 #pragma once
+#include <cstring>
 #include <map>
 #include <string>
 #include <unordered_map>
@@ -73,12 +74,22 @@ class Flattener {
  private:
   FlatScene out_;
   std::unordered_map<const Xf*, int32_t> xf_by_ptr_;
-  std::unordered_map<std::string, int32_t> xf_by_bits_, mat_by_bits_, pat_by_bits_, class_by_bits_;
+  std::unordered_map<std::string, int32_t> xf_by_bits_, mat_by_bits_, pat_by_bits_;
   std::unordered_map<const Material*, int32_t> mat_by_ptr_;
+  const Xf* last_xf_ = nullptr;
+  const Material* last_mat_ = nullptr;
+  int32_t last_xf_id_ = -1, last_mat_id_ = -1;
 
   static void put(std::string& k, const void* p, size_t n) { k.append((const char*)p, n); }
 
   int32_t xform_id(const XfP& x) {
+    if (x.get() == last_xf_) return last_xf_id_;  // runs of triangles share one Xf
+    const int32_t id = xform_lookup(x);
+    last_xf_ = x.get();
+    last_xf_id_ = id;
+    return id;
+  }
+  int32_t xform_lookup(const XfP& x) {
     auto it = xf_by_ptr_.find(x.get());
     if (it != xf_by_ptr_.end()) return it->second;
     std::string key((const char*)x->inv.m, 12 * sizeof(double));
@@ -110,6 +121,13 @@ class Flattener {
     return id;
   }
   int32_t material_id(const MaterialP& m) {
+    if (m.get() == last_mat_) return last_mat_id_;
+    const int32_t id = material_lookup(m);
+    last_mat_ = m.get();
+    last_mat_id_ = id;
+    return id;
+  }
+  int32_t material_lookup(const MaterialP& m) {
     auto it = mat_by_ptr_.find(m.get());
     if (it != mat_by_ptr_.end()) return it->second;
     rtc_material rm;
@@ -137,24 +155,89 @@ class Flattener {
     out_.boxes.insert(out_.boxes.end(), v, v + 6);
     return id;
   }
-  // exact-bit equality class of a leaf
+  // exact-bit equality class of a leaf: an open-addressing table keyed by a hash of everything the
+  // reference's PartialEq compares; a hash match is confirmed field by field against the earlier shape,
+  // so classes are exact and a million-triangle mesh costs no per-leaf allocation.
+  struct ClassEntry {
+    const Shape* s = nullptr;
+    int32_t xf = 0, mat = 0, id = 0;
+    uint64_t hash = 0;
+  };
+  std::vector<ClassEntry> class_slots_;
+  size_t class_count_ = 0;
+
+  static uint64_t mix(uint64_t h, const void* p, size_t n) {
+    const unsigned char* c = (const unsigned char*)p;
+    for (; n >= 8; n -= 8, c += 8) {
+      uint64_t w;
+      std::memcpy(&w, c, 8);
+      h = (h ^ w) * 0x9E3779B97F4A7C15ull;
+      h ^= h >> 29;
+    }
+    if (n) {
+      uint64_t w = 0;
+      std::memcpy(&w, c, n);
+      h = (h ^ w) * 0x9E3779B97F4A7C15ull;
+      h ^= h >> 29;
+    }
+    return h;
+  }
+  static void box6(const Shape& s, double bb[6]) {
+    bb[0] = s.box.min.x; bb[1] = s.box.min.y; bb[2] = s.box.min.z;
+    bb[3] = s.box.max.x; bb[4] = s.box.max.y; bb[5] = s.box.max.z;
+  }
+  static bool same_bits(const void* a, const void* b, size_t n) { return std::memcmp(a, b, n) == 0; }
+  static bool same_class(const Shape& a, int32_t axf, int32_t amat, const ClassEntry& e) {
+    const Shape& b = *e.s;
+    if (a.kind != b.kind || axf != e.xf || amat != e.mat || a.shadow != b.shadow) return false;
+    if (!same_bits(a.xf->m.m, b.xf->m.m, sizeof a.xf->m.m)) return false;
+    double ba[6], bb[6];
+    box6(a, ba);
+    box6(b, bb);
+    if (!same_bits(ba, bb, sizeof ba)) return false;
+    if (a.kind == RTC_CYLINDER || a.kind == RTC_CONE) {
+      if (!same_bits(&a.minimum, &b.minimum, 8) || !same_bits(&a.maximum, &b.maximum, 8) || a.closed != b.closed) return false;
+    }
+    if ((a.tri != nullptr) != (b.tri != nullptr)) return false;
+    if (a.tri && !same_bits(a.tri.get(), b.tri.get(), sizeof(TriData))) return false;
+    return true;
+  }
+  void class_grow() {
+    std::vector<ClassEntry> old;
+    old.swap(class_slots_);
+    class_slots_.assign(old.empty() ? 1024 : old.size() * 2, ClassEntry());
+    const size_t mask = class_slots_.size() - 1;
+    for (const ClassEntry& e : old) {
+      if (!e.s) continue;
+      size_t k = (size_t)e.hash & mask;
+      while (class_slots_[k].s) k = (k + 1) & mask;
+      class_slots_[k] = e;
+    }
+  }
   int32_t class_id(const Shape& s, int32_t xf, int32_t mat) {
-    std::string key;
-    int32_t head[4] = {s.kind, xf, mat, s.shadow ? 1 : 0};
-    put(key, head, sizeof head);
-    put(key, s.xf->m.m, sizeof s.xf->m.m);
-    const double bb[6] = {s.box.min.x, s.box.min.y, s.box.min.z, s.box.max.x, s.box.max.y, s.box.max.z};
-    put(key, bb, sizeof bb);
+    if ((class_count_ + 1) * 2 > class_slots_.size()) class_grow();
+    const int32_t head[4] = {s.kind, xf, mat, s.shadow ? 1 : 0};
+    uint64_t h = mix(0x243F6A8885A308D3ull, head, sizeof head);
+    h = mix(h, s.xf->m.m, sizeof s.xf->m.m);
+    double bb[6];
+    box6(s, bb);
+    h = mix(h, bb, sizeof bb);
     if (s.kind == RTC_CYLINDER || s.kind == RTC_CONE) {
       const double lim[3] = {s.minimum, s.maximum, s.closed ? 1.0 : 0.0};
-      put(key, lim, sizeof lim);
+      h = mix(h, lim, sizeof lim);
     }
-    if (s.tri) put(key, s.tri.get(), sizeof(TriData));
-    auto it = class_by_bits_.find(key);
-    if (it != class_by_bits_.end()) return it->second;
-    int32_t id = (int32_t)class_by_bits_.size();
-    class_by_bits_.emplace(std::move(key), id);
-    return id;
+    if (s.tri) h = mix(h, s.tri.get(), sizeof(TriData));
+    const size_t mask = class_slots_.size() - 1;
+    size_t k = (size_t)h & mask;
+    while (class_slots_[k].s) {
+      if (class_slots_[k].hash == h && same_class(s, xf, mat, class_slots_[k])) return class_slots_[k].id;
+      k = (k + 1) & mask;
+    }
+    ClassEntry e;
+    e.s = &s; e.xf = xf; e.mat = mat; e.id = (int32_t)class_count_; e.hash = h;
+    class_slots_[k] = e;
+    class_count_++;
+    return e.id;
   }
 
   void emit(const Shape& s) {

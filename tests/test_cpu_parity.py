@@ -29,3 +29,19 @@ def test_kernel_source_matches_oracle(case, pkg, prod, orc, emul):
     got2, ig2 = emul.render(cp, wp, aa=aa, faithful=False)
     assert np.array_equal(got, got2)
     assert ig2["rays"] == ig["rays"]
+
+
+@pytest.mark.parametrize("case", MESH_CASES, ids=case_id)
+def test_threaded_bvh_build_matches_oracle(case, pkg, prod, orc, emul, monkeypatch):
+    """The accelerator builder bins large ranges on worker threads and builds independent subtrees
+    in parallel (rt_accel_build.hpp); RTC_BVH_PAR_MIN pushes these small meshes through that path.
+    The frame must still be the oracle's, bit for bit — the search result never depends on the tree."""
+    name, kw, aa = case
+    wo, co = scenes.CONFIGS[name](orc.api, **kw)
+    wp, cp = scenes.CONFIGS[name](prod, **kw)
+    want, iw = orc.render(co, wo, aa=aa, threads=0)
+    monkeypatch.setenv("RTC_BVH_PAR_MIN", "16")
+    got, ig = emul.render(cp, wp, aa=aa, faithful=False)
+    assert ig["rays"] == iw["rays"]
+    frac, max8, lin = compare_images(got, want, orc.quantize)
+    assert frac == 1.0 and max8 == 0 and lin <= 1e-12
