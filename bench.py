@@ -309,10 +309,22 @@ def main():
                 traffic = json.load(fh).get(args.workload, {}).get("dram_bytes_per_launch")
         except Exception:
             traffic = None
+        flops_source = "counted by the oracle in this run"
+        if flops_frame is None:  # cpu_baseline leg skipped: the oracle's committed per-ray figure for this workload
+            try:
+                with open(os.path.join(ROOT, "profiles", "algorithmic_flops.json")) as fh:
+                    fpr = json.load(fh).get(args.workload)
+                if fpr:
+                    flops_frame = float(fpr) * rays_frame
+                    flops_source = "profiles/algorithmic_flops.json (oracle count of an earlier N=1 run) x rays of this run"
+            except Exception:
+                pass
         if flops_frame is not None:
             achieved = flops_frame / (ms_per_step * 1e-3) / 1e12
+            peak_nofma *= world_size   # whole-job achieved against the N-GPU roof (rank 0's measured peak x N)
+            peak_fma *= world_size
             roofline = {"bound": "fp64", "achieved": achieved, "peak": peak_nofma / 1e3, "unit": "TFLOP/s",
-                        "frac": achieved / (peak_nofma / 1e3), "traffic": traffic,
+                        "frac": achieved / (peak_nofma / 1e3), "traffic": traffic, "flops_source": flops_source,
                         "peak_source": "measured in this run: rtc_measure_fp64 (DMUL+DADD stream, non-fused — the library is built --fmad=false); MEASURED_PEAKS.json has no FP64 figure",
                         "peak_dfma_tflops": peak_fma / 1e3, "frac_of_dfma_peak": achieved / (peak_fma / 1e3),
                         "algorithmic_flops_per_frame": flops_frame,

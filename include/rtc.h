@@ -142,6 +142,10 @@ typedef struct rtc_opts {
 
 #define RTC_OPT_FAITHFUL_TRAVERSAL 1u /* disable the t-range box culling; visit exactly what
                                          Group::intersect (group.rs:49-58) visits */
+#define RTC_OPT_WAVEFRONT 4u          /* force the level-synchronous wavefront renderer (one work item per
+                                         color_at call; aa_samples == 1 only) ...                          */
+#define RTC_OPT_RECURSIVE 8u          /* ... or the one-thread-per-pixel kernel; neither: the library picks.
+                                         Both produce the same bits. */
 #define RTC_OPT_AVERAGE 2u            /* render_multithreaded semantics even for aa_samples == 1:
                                          Color::average = (0 + c) * (1.0/1) (camera.rs:186) */
 

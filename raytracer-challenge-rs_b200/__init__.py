@@ -27,6 +27,8 @@ HOST_LIB = os.path.join(_HERE, "host", "librth_host.so")
 
 RTC_OPT_FAITHFUL_TRAVERSAL = 1
 RTC_OPT_AVERAGE = 2
+RTC_OPT_WAVEFRONT = 4
+RTC_OPT_RECURSIVE = 8
 
 
 class RtcNode(C.Structure):
@@ -159,12 +161,14 @@ def _check(rc):
     return rc
 
 
-def make_opts(aa=1, max_depth=5, rows=None, tile_rows=8, rank=0, nranks=1, faithful=False, average=False):
+def make_opts(aa=1, max_depth=5, rows=None, tile_rows=8, rank=0, nranks=1, faithful=False, average=False, wavefront=None):
     o = RtcOpts()
     o.aa_samples, o.max_depth = aa, max_depth
     o.row_begin, o.row_end = (rows if rows else (0, 0))
     o.tile_rows, o.rank, o.nranks = tile_rows, rank, nranks
     o.flags = (RTC_OPT_FAITHFUL_TRAVERSAL if faithful else 0) | (RTC_OPT_AVERAGE if average else 0)
+    if wavefront is not None:  # None: the library's default; True/False force one renderer (same bits either way)
+        o.flags |= RTC_OPT_WAVEFRONT if wavefront else RTC_OPT_RECURSIVE
     return o
 
 

@@ -58,6 +58,17 @@ struct LeafRec {     // 96 bytes: one BVH prim (any bounded leaf shape), in BVH 
 
 static_assert(sizeof(PrimRec) == 128 && sizeof(LeafRec) == 96 && sizeof(BvhNode) == 128, "record layout");
 
+// World-space bounding sphere of an every-ray sphere prim (the first SPH_CULL_MAX of them; there are at
+// most BVH_MIN_PRIMS - 1 unless a transform is degenerate). Travels inside SceneView, i.e. in the
+// kernel's parameter (constant) bank. r2 = +inf disables the cull for that prim.
+constexpr int SPH_CULL_MAX = 8;
+struct SphCull {
+  double cx, cy, cz;  // centre = forward transform of the object-space origin
+  double r2;          // ||M^T M||_inf * (1 + 1e-4) >= sigma_max(M)^2 of the forward 3x3 M, padded
+  double far2;        // the cull is only trusted for |o - c|^2 < far2 (rounding of either side stays far below the pad)
+  double _pad;
+};
+
 struct AccelBuild {
   std::vector<LeafRec> leaf_recs;  // one per BVH prim: prims[n_always + k] ↔ leaf_recs[k]
   std::vector<PrimRec> recs;       // one per always-prim, same order as prims[0, n_always)
@@ -67,6 +78,7 @@ struct AccelBuild {
   int32_t n_sph = 0, n_pl = 0;     // the always-prefix is ordered spheres, planes, everything else
   std::vector<BvhNode> bvh;        // node 0 = root (empty vector: no BVH)
   int32_t max_depth = 0;
+  SphCull sph_cull[SPH_CULL_MAX];
 };
 
 namespace accel_detail {
@@ -481,6 +493,34 @@ inline void fill_recs(const rtc_scene_desc* d, AccelBuild& A) {
     r.kind_flags = ((uint32_t)nd.kind << 24) | (nd.flags & 0xffffffu);
     if (nd.kind != RTC_CSG)
       for (int c = 0; c < 12; c++) r.inv[c] = d->xforms[12 * (size_t)nd.xform + c];
+  }
+  // Bounding spheres for the sphere prefix. A ray whose line stays outside the padded bounding sphere
+  // has, in the reference's object space, a discriminant below -4a * 1e-4 — six orders of magnitude
+  // beyond what f64 rounding can flip while |o - c|^2 < far2 = 1e6 / ||inv||_F^2 (object-space distance
+  // below 1e3 radii) and the centre is not astronomically far from the world origin in object units.
+  for (int k = 0; k < SPH_CULL_MAX; k++) A.sph_cull[k] = SphCull{0.0, 0.0, 0.0, HUGE_VAL, 0.0, 0.0};
+  for (int32_t k = 0; k < A.n_sph && k < SPH_CULL_MAX; k++) {
+    const double* inv = A.recs[(size_t)k].inv;
+    double fwd[12];
+    if (!accel_detail::invert_affine(inv, fwd)) continue;
+    // sigma_max(M)^2 = rho(M^T M) <= ||M^T M||_inf (largest absolute row sum): tight for rotations times a
+    // uniform scale, where the Frobenius norm would overshoot by sqrt(3)
+    double f2 = 0.0, i2 = 0.0;
+    for (int r = 0; r < 3; r++) {
+      double row = 0.0;
+      for (int c = 0; c < 3; c++) {
+        double g = 0.0;
+        for (int m = 0; m < 3; m++) g += fwd[4 * m + r] * fwd[4 * m + c];
+        row += std::fabs(g);
+        i2 += inv[4 * r + c] * inv[4 * r + c];
+      }
+      f2 = std::max(f2, row);
+    }
+    const double cx = fwd[3], cy = fwd[7], cz = fwd[11];
+    const double c2 = cx * cx + cy * cy + cz * cz;
+    if (!std::isfinite(f2) || !std::isfinite(i2) || !std::isfinite(c2) || !(i2 > 0.0) || !(f2 > 0.0)) continue;
+    if (i2 * c2 > 1e12) continue;  // ||inv||_F * |c| > 1e6: translation cancellation in the reference's own o_obj
+    A.sph_cull[k] = SphCull{cx, cy, cz, f2 * (1.0 + 1e-4), 1e6 / i2, 0.0};
   }
 }
 

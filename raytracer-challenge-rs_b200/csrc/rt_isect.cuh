@@ -37,6 +37,7 @@ struct SceneView {
   int32_t n_bvh;             // BVH node count (0: no BVH)
   int32_t n_sph, n_pl;       // always-prefix: [0,n_sph) spheres, [n_sph,n_sph+n_pl) planes, then the rest
   int32_t _pad;
+  SphCull sph_cull[SPH_CULL_MAX];  // bounding spheres of the first every-ray spheres (parameter bank)
 };
 
 RTC_HD void slab_axis(double origin, double direction, double mn, double mx, double& tmin, double& tmax) {

@@ -21,6 +21,7 @@ struct RenderParams {
   uint32_t aa, average;
   int32_t max_depth;
   uint32_t faithful;             // RTC_OPT_FAITHFUL_TRAVERSAL: the reference's own search order
+  uint32_t flags;                // rtc_opts.flags
 };
 
 // counters[0..3] rays primary/shadow/reflect/refract, [4] overflow pixels, [5] NaN pixels

@@ -289,9 +289,11 @@ struct Tracer {
   V3 result;
   double t_primary;
   int sp, remaining, li, phase;
+  bool w_emit;  // wavefront mode (rt_wave.cuh): this call needs children and has handed them to `emit`
 
   RTC_HD void start(const RayD& r, int max_depth, Frame* frames, uint32_t* err) {
     (void)frames;
+    w_emit = false;
     cur.ray = r;
     qray = r;
     sp = 0;
@@ -304,7 +306,11 @@ struct Tracer {
 
   // Consume the answer of the pending query; set up the next one. Returns true when color_at of the
   // primary ray is complete (`result`).
-  RTC_HD bool advance(const SceneView& S, Frame* frames, HitList& neg, RayCounters& rc, uint32_t* err) {
+  // WAVE (rt_wave.cuh): a call that needs children does not descend; it hands the suspended shade_hit
+  // and the reflection ray to `emit` (the refraction ray is f.refr_ray) and reports completion.
+  struct NoEmit { RTC_HD void operator()(const Frame&, const RayD&, bool) const {} };
+  template <bool WAVE = false, class EmitFn = NoEmit>
+  RTC_HD bool advance(const SceneView& S, Frame* frames, HitList& neg, RayCounters& rc, uint32_t* err, EmitFn emit = EmitFn()) {
     int next;
     V3 res = v3(0.0, 0.0, 0.0);
     double n1 = -1.0, n2 = -1.0;
@@ -396,7 +402,8 @@ struct Tracer {
         }
       }
       if (want_reflect || need_refract) {
-        Frame& f = frames[sp];
+        Frame wave_f;
+        Frame& f = WAVE ? wave_f : frames[sp];
         f.surface = cur.surface;
         f.reflected = v3(0.0, 0.0, 0.0);
         f.refr_ray = refr;
@@ -415,6 +422,12 @@ struct Tracer {
           child = refr;
         }
         descend = true;
+        if (WAVE) {  // both children are known now: emit them instead of descending
+          if (want_reflect && need_refract) rc.refract++;
+          emit(f, child, want_reflect);
+          w_emit = true;
+          return true;
+        }
       } else {
         res = combine(cur.surface, v3(0.0, 0.0, 0.0), v3(0.0, 0.0, 0.0), reflectance, use_schlick);
       }

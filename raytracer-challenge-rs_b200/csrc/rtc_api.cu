@@ -11,7 +11,7 @@
 #include <string>
 #include <vector>
 
-#include "rt_kernels.cuh"
+#include "rt_wave.cuh"
 
 using namespace rtk;
 
@@ -32,6 +32,9 @@ int fail(int code, const std::string& msg) {
   } while (0)
 
 constexpr int N_COUNTERS = 8;
+#ifndef RTK_WAVE_DEFAULT
+#define RTK_WAVE_DEFAULT 0
+#endif
 
 }  // namespace
 
@@ -49,6 +52,15 @@ struct rtc_scene {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   uint32_t launches = 0;
+  int sm_count = 148;
+  // wavefront path (rt_wave.cuh): queue arena, and what rtc_scene_finish needs to redo the frame with
+  // the recursive kernel should a queue have overflowed
+  char* wave_arena = nullptr;
+  size_t wave_bytes = 0;
+  bool last_wave = false;
+  CameraD last_cam{};
+  RenderParams last_P{};
+  double* last_out = nullptr;
 };
 
 struct rtc_canvas {
@@ -166,6 +178,7 @@ int make_params(const rtc_camera* c, const rtc_opts* o, RenderParams& P, bool& f
   P.aa = d.aa_samples;
   P.average = (d.aa_samples > 1 || (d.flags & RTC_OPT_AVERAGE)) ? 1u : 0u;
   P.max_depth = (int32_t)d.max_depth;
+  P.flags = d.flags;
   faithful = (d.flags & RTC_OPT_FAITHFUL_TRAVERSAL) != 0;
   return RTC_OK;
 }
@@ -195,10 +208,164 @@ int launch_rows(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool fa
   return RTC_OK;
 }
 
+// Scratch arenas are big (GBs at 4K): keep one freed arena per device, like the canvases.
+struct ArenaPool {
+  std::mutex mu;
+  char* ptr[16] = {nullptr};
+  size_t bytes[16] = {0};
+  char* take(int dev, size_t need, size_t& got) {
+    std::lock_guard<std::mutex> g(mu);
+    if (dev >= 0 && dev < 16 && ptr[dev] && bytes[dev] >= need) {
+      char* p = ptr[dev];
+      got = bytes[dev];
+      ptr[dev] = nullptr;
+      bytes[dev] = 0;
+      return p;
+    }
+    return nullptr;
+  }
+  void give(int dev, char* p, size_t n) {
+    {
+      std::lock_guard<std::mutex> g(mu);
+      if (dev >= 0 && dev < 16 && bytes[dev] < n) {
+        std::swap(ptr[dev], p);
+        std::swap(bytes[dev], n);
+      }
+    }
+    if (p) cudaFree(p);
+  }
+};
+ArenaPool g_arena_pool;
+
+int ensure_arena(rtc_scene* s, size_t need) {
+  if (s->wave_bytes >= need) return RTC_OK;
+  if (s->wave_arena) g_arena_pool.give(s->device, s->wave_arena, s->wave_bytes);
+  s->wave_arena = nullptr;
+  s->wave_bytes = 0;
+  size_t got = 0;
+  s->wave_arena = g_arena_pool.take(s->device, need, got);
+  if (s->wave_arena) {
+    s->wave_bytes = got;
+  } else {
+    CUDA_TRY(cudaMalloc((void**)&s->wave_arena, need));
+    s->wave_bytes = need;
+  }
+  return RTC_OK;
+}
+
+template <bool HAS_CSG, int MINB>
+void launch_wave_level(rtc_scene* s, const CameraD& cam, const RenderParams& P, const WaveArgs& A, bool primary, double* out,
+                       cudaStream_t stream) {
+  const int grid = s->sm_count * MINB;
+  if (primary) wave_forward_kernel<HAS_CSG, true, MINB><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+  else wave_forward_kernel<HAS_CSG, false, MINB><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+  s->launches++;
+}
+
+// The frame as a level-synchronous wavefront (rt_wave.cuh): 1 + max_depth forward passes and max_depth
+// combine passes, queued back to back; no host synchronisation in between.
+int launch_wave(rtc_scene* s, const CameraD& cam, const RenderParams& P, double* out, cudaStream_t stream) {
+  const int D = P.max_depth;
+  const size_t px = (size_t)P.owned_rows * cam.hsize;
+  if (px == 0) return RTC_OK;
+  if (px > 0x3fffffffu) return fail(RTC_ERR_UNSUPPORTED, "frame too large for the wavefront queues");
+  // capacities: level 0 has one call per pixel; deeper levels get 2 per pixel (worst case 2^L: overflow →
+  // counters[6] → rtc_scene_finish re-renders with the recursive kernel)
+  size_t off = 256;  // [0,256): uint32 n_items[16], n_recs[16], work[16]
+  struct Lay { size_t items, recs, child; uint32_t cap_items, cap_recs; } lay[WAVE_MAX_LEVELS + 1] = {};
+  for (int L = 0; L <= D; L++) {
+    lay[L].cap_items = L == 0 ? 0u : (uint32_t)(2 * px);
+    lay[L].cap_recs = L == D ? 0u : (L == 0 ? (uint32_t)px : (uint32_t)(2 * px));
+    lay[L].items = off; off += align_up((size_t)lay[L].cap_items * sizeof(WaveItem));
+    lay[L].recs = off; off += align_up((size_t)lay[L].cap_recs * sizeof(WaveRec));
+    lay[L].child = off; off += align_up((size_t)lay[L].cap_recs * 6 * sizeof(double));
+  }
+  int rc = ensure_arena(s, off);
+  if (rc) return rc;
+  char* base = s->wave_arena;
+  uint32_t* n_items = (uint32_t*)base;
+  uint32_t* n_recs = n_items + 16;
+  uint32_t* work = n_items + 32;
+  CUDA_TRY(cudaMemsetAsync(base, 0, 256, stream));
+  auto level = [&](int L) {
+    WaveLevel w{};
+    if (L > D) return w;
+    w.items = (WaveItem*)(base + lay[L].items);
+    w.recs = (WaveRec*)(base + lay[L].recs);
+    w.child = (double*)(base + lay[L].child);
+    w.cap_items = lay[L].cap_items;
+    w.cap_recs = lay[L].cap_recs;
+    return w;
+  };
+  for (int L = 0; L <= D; L++) {
+    WaveArgs A{};
+    A.cur = level(L);
+    A.next = level(L + 1);
+    A.n_items_cur = n_items + L;
+    A.n_recs_cur = n_recs + L;
+    A.n_items_next = n_items + L + 1;
+    A.work = work + L;
+    A.parent_child = L > 0 ? level(L - 1).child : nullptr;
+    A.remaining = D - L;
+    if (s->has_csg) {
+      if (s->big_accel) launch_wave_level<true, 8>(s, cam, P, A, L == 0, out, stream);
+      else launch_wave_level<true, RTK_MIN_BLOCKS>(s, cam, P, A, L == 0, out, stream);
+    } else {
+      if (s->big_accel) launch_wave_level<false, 8>(s, cam, P, A, L == 0, out, stream);
+      else launch_wave_level<false, RTK_MIN_BLOCKS>(s, cam, P, A, L == 0, out, stream);
+    }
+  }
+  for (int L = D - 1; L >= 0; L--) {
+    const WaveLevel w = level(L);
+    const int grid = s->sm_count * 4;
+    if (L == 0) wave_combine_kernel<true><<<grid, 256, 0, stream>>>(w.recs, w.child, n_recs + L, w.cap_recs, nullptr, out, s->d_counters);
+    else wave_combine_kernel<false><<<grid, 256, 0, stream>>>(w.recs, w.child, n_recs + L, w.cap_recs, level(L - 1).child, out, s->d_counters);
+    s->launches++;
+  }
+  CUDA_TRY(cudaGetLastError());
+  return RTC_OK;
+}
+
+// RTC_WAVEFRONT=0/1 in the environment overrides the choice (experiments); otherwise RTC_OPT_WAVEFRONT /
+// RTC_OPT_RECURSIVE in rtc_opts.flags, otherwise the measured default.
+bool use_wavefront(const RenderParams& P, bool faithful, uint32_t flags) {
+  if (faithful || P.aa != 1 || P.average || P.max_depth < 1) return false;
+  static const char* env = std::getenv("RTC_WAVEFRONT");
+  if (env && env[0] == '0') return false;
+  if (env && env[0] == '1') return true;
+  if (flags & RTC_OPT_RECURSIVE) return false;
+  if (flags & RTC_OPT_WAVEFRONT) return true;
+  return RTK_WAVE_DEFAULT != 0;
+}
+
 int launch_frame(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool faithful, double* out, cudaStream_t stream) {
   CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, N_COUNTERS * sizeof(unsigned long long), stream));
   CUDA_TRY(cudaEventRecord(s->ev0, stream));
-  int rc = launch_rows(s, cam, P, faithful, out, stream, 0, 0);
+  s->last_wave = use_wavefront(P, faithful, P.flags);
+  int rc;
+  if (s->last_wave) {
+    s->last_cam = cam; s->last_P = P; s->last_out = out;
+    rc = launch_wave(s, cam, P, out, stream);
+  } else {
+    rc = launch_rows(s, cam, P, faithful, out, stream, 0, 0);
+  }
+  if (rc) return rc;
+  CUDA_TRY(cudaEventRecord(s->ev1, stream));
+  return RTC_OK;
+}
+
+// A wavefront frame whose queues were too small (more than 2 calls per pixel at some level) is rendered
+// again by the recursive kernel, which needs no queues. Must run before anything reads the canvas.
+int resolve_wave(rtc_scene* s, cudaStream_t stream) {
+  if (!s->last_wave) return RTC_OK;
+  s->last_wave = false;
+  unsigned long long dropped = 0;
+  CUDA_TRY(cudaMemcpyAsync(&dropped, s->d_counters + 6, sizeof dropped, cudaMemcpyDeviceToHost, stream));
+  CUDA_TRY(cudaStreamSynchronize(stream));
+  if (!dropped) return RTC_OK;
+  CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, N_COUNTERS * sizeof(unsigned long long), stream));
+  CUDA_TRY(cudaEventRecord(s->ev0, stream));
+  int rc = launch_rows(s, s->last_cam, s->last_P, false, s->last_out, stream, 0, 0);
   if (rc) return rc;
   CUDA_TRY(cudaEventRecord(s->ev1, stream));
   return RTC_OK;
@@ -315,6 +482,7 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
     }
   }
   if ((e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+  { int n = 0; if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && n > 0) s->sm_count = n; }
   const size_t tail = align_up(N_COUNTERS * sizeof(unsigned long long)) + align_up(32 * sizeof(double));
   if ((e = cudaMallocAsync((void**)&s->slab, total + tail, s->stream)) != cudaSuccess) return bail(e, "cudaMallocAsync(scene)");
   s->d_counters = (unsigned long long*)(s->slab + total);
@@ -363,6 +531,7 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   v.n_always = accel.n_always;
   v.n_sph = accel.n_sph;
   v.n_pl = accel.n_pl;
+  for (int k = 0; k < SPH_CULL_MAX; k++) v.sph_cull[k] = accel.sph_cull[k];
   v.n_bvh = (int32_t)accel.bvh.size();
   v.n_nodes = (int32_t)d->n_nodes;
   v.n_lights = (int32_t)d->n_lights;
@@ -378,7 +547,7 @@ void rtc_scene_destroy(rtc_scene* s) {
     if (s->stream) cudaFreeAsync(s->slab, s->stream); else cudaFree(s->slab);
   }
   if (s->d_canvas) g_canvas_pool.give(s->device, s->d_canvas, s->canvas_doubles);
-
+  if (s->wave_arena) g_arena_pool.give(s->device, s->wave_arena, s->wave_bytes);
   if (s->ev0) cudaEventDestroy(s->ev0);
   if (s->ev1) cudaEventDestroy(s->ev1);
   if (s->stream) cudaStreamDestroy(s->stream);
@@ -412,7 +581,9 @@ int rtc_scene_finish(rtc_scene* s, void* stream_, rtc_stats* stats) {
   CUDA_TRY(cudaSetDevice(s->device));
   cudaStream_t stream = (cudaStream_t)stream_;
   if (stats) std::memset(stats, 0, sizeof *stats);
-  int rc = read_counters(s, stream, stats);
+  int rc = resolve_wave(s, stream);
+  if (rc) return rc;
+  rc = read_counters(s, stream, stats);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(RTC_ERR_CUDA, std::string("kernel: ") + cudaGetErrorString(e));
   if (stats) {
@@ -458,7 +629,10 @@ int rtc_render(rtc_scene* s, const rtc_camera* camera, const rtc_opts* opts, dou
     // it over PCIe (24 B per pixel, posted writes spread over the whole kernel) and there is no
     // device canvas and no device→host copy at all.
     cudaPointerAttributes attr;
-    if (cudaPointerGetAttributes(&attr, rgb_host) == cudaSuccess && attr.type == cudaMemoryTypeHost && attr.devicePointer) {
+    // (The wavefront renderer writes a pixel from whichever pass completes it; measured over PCIe that is
+    // 9.8 ms against 3.9 ms into a device canvas, so it takes the staged path: device canvas, one DMA.)
+    if (!use_wavefront(P, faithful, P.flags) && cudaPointerGetAttributes(&attr, rgb_host) == cudaSuccess &&
+        attr.type == cudaMemoryTypeHost && attr.devicePointer) {
       s->launches = 0;
       rc = launch_frame(s, cam, P, faithful, (double*)attr.devicePointer, s->stream);
       if (rc) return rc;
@@ -477,10 +651,14 @@ int rtc_render(rtc_scene* s, const rtc_camera* camera, const rtc_opts* opts, dou
   if (P.nranks <= 1) {
     rc = launch_frame(s, cam, P, faithful, s->d_canvas, s->stream);
     if (rc) return rc;
+    rc = resolve_wave(s, s->stream);  // before the canvas is read
+    if (rc) return rc;
     size_t off = (size_t)P.row_begin * row_doubles, cnt = (size_t)(P.row_end - P.row_begin) * row_doubles;
     if (cnt) CUDA_TRY(cudaMemcpyAsync(rgb_host + off, s->d_canvas + off, cnt * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
   } else {
     rc = launch_frame(s, cam, P, faithful, s->d_canvas, s->stream);
+    if (rc) return rc;
+    rc = resolve_wave(s, s->stream);  // before the canvas is read
     if (rc) return rc;
     // device → host: only the rows this call rendered (owned tiles clipped to the row range)
     for (uint32_t t = P.rank; (size_t)t * P.tile_rows < cam.vsize; t += P.nranks) {
@@ -528,6 +706,8 @@ int rtc_render_rgb8(rtc_scene* s, const rtc_camera* camera, const rtc_opts* opts
   if (rc) return rc;
   s->launches = 0;
   rc = launch_frame(s, cam, P, faithful, s->d_canvas, s->stream);
+  if (rc) return rc;
+  rc = resolve_wave(s, s->stream);  // before the canvas is read
   if (rc) return rc;
   const size_t off = (size_t)P.row_begin * cam.hsize * 3, cnt = (size_t)(P.row_end - P.row_begin) * cam.hsize * 3;
   if (cnt) {

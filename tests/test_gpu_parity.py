@@ -52,6 +52,51 @@ def test_culling_is_bit_neutral(case, pkg, prod):
     ds.close()
 
 
+@pytest.mark.parametrize("case", [c for c in SMALL_CASES + MESH_CASES if c[2] == 1], ids=case_id)
+def test_wavefront_is_bit_identical(case, pkg, prod):
+    """The level-synchronous wavefront renderer (rt_wave.cuh: one work item per color_at call) vs the
+    one-thread-per-pixel kernel: same bits, same per-kind ray counts; also sharded (cyclic tiles) and into
+    a pinned host canvas, and with max_depth 0 (no children at all) and 2."""
+    name, kw, aa = case
+    wp, cp = scenes.CONFIGS[name](prod, **kw)
+    ds = pkg.DeviceScene(pkg.FlatScene(wp))
+    for depth in (5, 0, 2):
+        a, sa = ds.render(cp, aa=1, max_depth=depth, wavefront=False)
+        b, sb = ds.render(cp, aa=1, max_depth=depth, wavefront=True)
+        assert sb.launches == (2 * depth + 1 if depth > 0 else 1) and sa.launches == 1
+        assert np.array_equal(a, b), depth
+        assert (sa.rays_primary, sa.rays_shadow, sa.rays_reflect, sa.rays_refract) == \
+            (sb.rays_primary, sb.rays_shadow, sb.rays_reflect, sb.rays_refract), depth
+    full, _ = ds.render(cp, aa=1, wavefront=False)
+    parts = np.zeros_like(full)
+    for r in range(3):
+        ds.render(cp, out=parts, aa=1, tile_rows=4, rank=r, nranks=3, wavefront=True)
+    assert np.array_equal(full, parts)
+    ds.close()
+
+
+def test_wavefront_queue_overflow_falls_back(pkg, prod):
+    """Nested glass: every hit spawns a reflection AND a refraction ray, so a level needs more than the
+    2 queue slots per pixel; the frame must still come back complete and identical (re-rendered by the
+    recursive kernel inside rtc_scene_finish)."""
+    w = prod.world()
+    w.add_light((-4, 6, -8), (1, 1, 1))
+    for k in range(4):
+        s = prod.glass_sphere()
+        s.set_transform(pkg.transform.scaling(3.0 - 0.5 * k, 3.0 - 0.5 * k, 3.0 - 0.5 * k))
+        m = pkg.Material(color=(0.1, 0.1, 0.1), reflective=0.9, transparency=0.9, refractive_index=1.1 + 0.1 * k)
+        s.set_material(m)
+        w.add_object(s)
+    c = prod.camera(96, 64, 0.9)
+    c.set_transform(pkg.transform.view_transform((0, 0, -2.9), (0, 0, 0), (0, 1, 0)))
+    ds = pkg.DeviceScene(pkg.FlatScene(w))
+    a, sa = ds.render(c, wavefront=False)
+    b, sb = ds.render(c, wavefront=True)
+    assert np.array_equal(a, b) and sa.rays == sb.rays
+    assert sa.rays_reflect + sa.rays_refract > 2 * 2 * 96 * 64  # some level really exceeded 2 per pixel
+    ds.close()
+
+
 def test_reference_known_answers_through_cabi(pkg, prod):
     """world.rs:186-234,249-274 and camera.rs:328-337 through rtc_trace_rays / rtc_is_shadowed."""
     w, c = scenes.default_world(prod)
