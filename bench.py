@@ -340,9 +340,10 @@ def main():
                 "config": {"workload": args.workload, "desc": desc, "width": W, "height": H, "aa": aa, "max_depth": 5,
                            "rays_per_frame": rays_frame, "l2": "flushed between frames (256 MB fill)",
                            "sharding": "cyclic %d-row tiles, gather=%s" % (args.tile_rows, sr.gather),
+                           "renderer": "wavefront (rt_wave.cuh), %d launches/frame" % st.launches if st.launches > 1 else "recursive kernel, 1 launch/frame",
                            "scene_bytes": flat.info["bytes"], "scene_build_ms": build_ms, "flatten_ms": flatten_ms,
                            "wall_ms_timed_region": wall_ms},
-                "e2e": e2e, "gpu_launches": args.steps * (1 if True else 0), "clocks": sampler.summary() if sampler else None,
+                "e2e": e2e, "gpu_launches": args.steps * int(st.launches), "clocks": sampler.summary() if sampler else None,
                 "roofline": roofline, "cpu_baseline": cpu_baseline}
         print(json.dumps(line), flush=True)
     sr.close()

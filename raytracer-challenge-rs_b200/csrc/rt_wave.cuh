@@ -54,13 +54,13 @@ struct WaveLevel {
   uint32_t cap_items, cap_recs;
 };
 struct WaveArgs {
-  WaveLevel cur, next;    // next.items / counters[next] receive the children
-  uint32_t* n_items_cur;  // device counters
-  uint32_t* n_recs_cur;
-  uint32_t* n_items_next;
-  uint32_t* work;         // this pass's work counter (items handed out so far)
-  double* parent_child;   // previous level's child slots (level 0: unused)
-  int32_t remaining;      // max_depth - level
+  WaveLevel lv[WAVE_MAX_LEVELS + 1];
+  uint32_t* n_items;      // device counters, one per level
+  uint32_t* n_recs;
+  uint32_t* work;         // per pass: items handed out so far
+  int32_t level;          // the level whose queue this pass drains
+  int32_t max_depth;
+  uint32_t inline_min;    // keep the first child in-lane when at least this many lanes of the warp emit (33: never)
   uint32_t _pad;
 };
 
@@ -78,9 +78,16 @@ struct WaveStage {
   uint32_t bits[128];
 };
 
-// One forward pass. PRIMARY: items are the pixels of this rank's tiles, a warp = one 8x4 patch.
-// Work is handed out 32 items at a time from a device counter (patches / queue slices differ in cost
-// by more than 10x; a static grid-stride split leaves most of the chip waiting for the unluckiest warp).
+// One forward pass over the queue of level A.level. PRIMARY: items are the pixels of this rank's tiles, a
+// warp = one 8x4 patch. Work is handed out 32 items at a time from a device counter (patches / queue
+// slices differ in cost by more than 10x; a static split leaves the chip waiting for the unluckiest warp).
+//
+// A call that needs children may KEEP one of them: the lane stores its WaveRec and carries on with the
+// reflection ray (the refraction ray when there is no reflection) as a call of the next level, in the
+// same pass — no queue round trip for mirror chains; only the second child of a glass hit is queued.
+// A thread's serial chain is then at most max_depth + 1 calls, against 2^(max_depth+1) - 1 recursively.
+// All lanes of a warp move down one level per step, so the level is warp-uniform. Keeping pays while
+// most of the warp carries on (A.inline_min); a sparse warp queues everything instead.
 template <bool HAS_CSG, bool PRIMARY, int MINB>
 __global__ void __launch_bounds__(128, MINB) wave_forward_kernel(SceneView S, CameraD cam, RenderParams P, WaveArgs A,
                                                                  double* __restrict__ canvas,
@@ -94,7 +101,7 @@ __global__ void __launch_bounds__(128, MINB) wave_forward_kernel(SceneView S, Ca
   uint32_t err = 0, dropped = 0;
   // patches: 8 px wide, 4 rows tall over the owned-row domain
   const uint32_t pw = (cam.hsize + 7u) >> 3, ph = (P.owned_rows + 3u) >> 2;
-  const uint32_t n = PRIMARY ? pw * ph * 32u : min(*A.n_items_cur, A.cur.cap_items);
+  const uint32_t n = PRIMARY ? pw * ph * 32u : min(A.n_items[A.level], A.lv[A.level].cap_items);
   // the next batch's index is requested before the current batch is processed: the atomic's round trip
   // to L2 overlaps the work instead of preceding it
   uint32_t next = 0;
@@ -120,81 +127,101 @@ __global__ void __launch_bounds__(128, MINB) wave_forward_kernel(SceneView S, Ca
         parent = py * cam.hsize + px;  // Canvas::pixel_idx, canvas.rs:44-48
       }
     } else if (active) {
-      const WaveItem* it = A.cur.items + idx;
+      const WaveItem* it = A.lv[A.level].items + idx;
       const double2* q = reinterpret_cast<const double2*>(it);
       const double2 a = __ldcs(q), b = __ldcs(q + 1), c = __ldcs(q + 2);
       const int4 h = __ldcs(reinterpret_cast<const int4*>(q + 3));
       ray.o = v3(a.x, a.y, b.x); ray.d = v3(b.y, c.x, c.y);
       parent = (uint32_t)h.x; slot = (uint32_t)h.y;
     }
-    bool emit = false;
-    V3 result = v3(0.0, 0.0, 0.0);
-    if (active) {
-      Tracer tr;
-      tr.start(ray, A.remaining, nullptr, &err);
-      auto put = [&](const Frame& f, const RayD& refl, bool has_reflect) {
-        stage.d[0][tid] = f.surface.x; stage.d[1][tid] = f.surface.y; stage.d[2][tid] = f.surface.z;
-        stage.d[3][tid] = f.reflective; stage.d[4][tid] = f.transparency; stage.d[5][tid] = f.reflectance;
-        stage.d[6][tid] = refl.o.x; stage.d[7][tid] = refl.o.y; stage.d[8][tid] = refl.o.z;
-        stage.d[9][tid] = refl.d.x; stage.d[10][tid] = refl.d.y; stage.d[11][tid] = refl.d.z;
-        stage.d[12][tid] = f.refr_ray.o.x; stage.d[13][tid] = f.refr_ray.o.y; stage.d[14][tid] = f.refr_ray.o.z;
-        stage.d[15][tid] = f.refr_ray.d.x; stage.d[16][tid] = f.refr_ray.d.y; stage.d[17][tid] = f.refr_ray.d.z;
-        stage.bits[tid] = f.bits | (has_reflect ? WR_HAS_REFLECT : 0u);
-      };
-      for (;;) {
-        search<HAS_CSG, false>(S, tr.qray, tr.q, scratch.csg(), &scratch.bvh, &err);
-        if (tr.template advance<true>(S, nullptr, scratch.neg, rc, &err, put)) break;
-      }
-      emit = tr.w_emit;
-      result = tr.result;
-    }
-    __syncwarp();
-    double* dst = PRIMARY ? canvas + (size_t)parent * 3 : A.parent_child + ((size_t)parent * 2 + slot) * 3;
-    if (active && !emit) wave_store_color(dst, result);
-    // warp-aggregated allocation: one record per emitting lane, reflection children first, then refraction
-    const uint32_t m_emit = __ballot_sync(0xffffffffu, emit);
-    if (m_emit == 0u) continue;
-    const uint32_t bits = emit ? stage.bits[tid] : 0u;
-    const bool c_refl = (bits & WR_HAS_REFLECT) != 0, c_refr = (bits & FR_NEED_REFRACT) != 0;
-    const uint32_t m_refl = __ballot_sync(0xffffffffu, c_refl), m_refr = __ballot_sync(0xffffffffu, c_refr);
-    const uint32_t n_refl = __popc(m_refl), n_child = n_refl + __popc(m_refr);
-    uint32_t rec0 = 0, item0 = 0;
-    if (lane == 0) {
-      rec0 = atomicAdd(A.n_recs_cur, (uint32_t)__popc(m_emit));
-      item0 = atomicAdd(A.n_items_next, n_child);
-    }
-    rec0 = __shfl_sync(0xffffffffu, rec0, 0);
-    item0 = __shfl_sync(0xffffffffu, item0, 0);
-    const uint32_t lt = (1u << lane) - 1u;
-    if (emit) {
-      const uint32_t ri = rec0 + __popc(m_emit & lt);
-      const uint32_t i_refl = item0 + __popc(m_refl & lt), i_refr = item0 + n_refl + __popc(m_refr & lt);
-      const bool fits = ri < A.cur.cap_recs && (!c_refl || i_refl < A.next.cap_items) && (!c_refr || i_refr < A.next.cap_items);
-      if (!fits) {
-        dropped++;
-      } else {
-        double2* R = reinterpret_cast<double2*>(A.cur.recs + ri);
-        R[0] = make_double2(stage.d[0][tid], stage.d[1][tid]);
-        R[1] = make_double2(stage.d[2][tid], stage.d[3][tid]);
-        R[2] = make_double2(stage.d[4][tid], stage.d[5][tid]);
-        reinterpret_cast<uint4*>(R)[3] = make_uint4(parent, slot, bits, 0u);
-        if (c_refl) {
-          double2* w = reinterpret_cast<double2*>(A.next.items + i_refl);
-          w[0] = make_double2(stage.d[6][tid], stage.d[7][tid]);
-          w[1] = make_double2(stage.d[8][tid], stage.d[9][tid]);
-          w[2] = make_double2(stage.d[10][tid], stage.d[11][tid]);
-          reinterpret_cast<uint4*>(w)[3] = make_uint4(ri, 0u, 0u, 0u);
+    for (int l = PRIMARY ? 0 : A.level;; l++) {  // the chain of kept children; l is warp-uniform
+      bool emit = false;
+      V3 result = v3(0.0, 0.0, 0.0);
+      if (active) {
+        Tracer tr;
+        tr.start(ray, A.max_depth - l, nullptr, &err);
+        auto put = [&](const Frame& f, const RayD& refl, bool has_reflect) {
+          stage.d[0][tid] = f.surface.x; stage.d[1][tid] = f.surface.y; stage.d[2][tid] = f.surface.z;
+          stage.d[3][tid] = f.reflective; stage.d[4][tid] = f.transparency; stage.d[5][tid] = f.reflectance;
+          stage.d[6][tid] = refl.o.x; stage.d[7][tid] = refl.o.y; stage.d[8][tid] = refl.o.z;
+          stage.d[9][tid] = refl.d.x; stage.d[10][tid] = refl.d.y; stage.d[11][tid] = refl.d.z;
+          stage.d[12][tid] = f.refr_ray.o.x; stage.d[13][tid] = f.refr_ray.o.y; stage.d[14][tid] = f.refr_ray.o.z;
+          stage.d[15][tid] = f.refr_ray.d.x; stage.d[16][tid] = f.refr_ray.d.y; stage.d[17][tid] = f.refr_ray.d.z;
+          stage.bits[tid] = f.bits | (has_reflect ? WR_HAS_REFLECT : 0u);
+        };
+        for (;;) {
+          search<HAS_CSG, false>(S, tr.qray, tr.q, scratch.csg(), &scratch.bvh, &err);
+          if (tr.template advance<true>(S, nullptr, scratch.neg, rc, &err, put)) break;
         }
-        if (c_refr) {
-          double2* w = reinterpret_cast<double2*>(A.next.items + i_refr);
-          w[0] = make_double2(stage.d[12][tid], stage.d[13][tid]);
-          w[1] = make_double2(stage.d[14][tid], stage.d[15][tid]);
-          w[2] = make_double2(stage.d[16][tid], stage.d[17][tid]);
-          reinterpret_cast<uint4*>(w)[3] = make_uint4(ri, 1u, 0u, 0u);
+        emit = tr.w_emit;
+        result = tr.result;
+      }
+      __syncwarp();
+      if (active && !emit) {
+        double* dst = l == 0 ? canvas + (size_t)parent * 3 : A.lv[l - 1].child + ((size_t)parent * 2 + slot) * 3;
+        wave_store_color(dst, result);
+      }
+      // warp-aggregated allocation: one record per emitting lane and a queue slot per queued child. The
+      // first child is KEPT (the lane carries on with it) only if at least A.inline_min lanes emit: a
+      // mostly idle warp is better off handing everything to the queue, where the next pass packs it.
+      const uint32_t m_emit = __ballot_sync(0xffffffffu, emit);
+      if (m_emit == 0u) break;
+      const bool keep = (uint32_t)__popc(m_emit) >= A.inline_min;
+      const uint32_t bits = emit ? stage.bits[tid] : 0u;
+      const bool has_refl = (bits & WR_HAS_REFLECT) != 0, has_refr = (bits & FR_NEED_REFRACT) != 0;
+      // queued: (reflection unless kept) and (refraction unless it is the kept first child)
+      const bool q_refl = has_refl && !keep, q_refr = has_refr && (has_refl || !keep);
+      const uint32_t m_qa = __ballot_sync(0xffffffffu, q_refl), m_qb = __ballot_sync(0xffffffffu, q_refr);
+      const uint32_t n_qa = __popc(m_qa);
+      uint32_t rec0 = 0, item0 = 0;
+      if (lane == 0) {
+        rec0 = atomicAdd(A.n_recs + l, (uint32_t)__popc(m_emit));
+        if (m_qa | m_qb) item0 = atomicAdd(A.n_items + l + 1, n_qa + (uint32_t)__popc(m_qb));
+      }
+      rec0 = __shfl_sync(0xffffffffu, rec0, 0);
+      item0 = __shfl_sync(0xffffffffu, item0, 0);
+      const uint32_t lt = (1u << lane) - 1u;
+      active = false;
+      if (emit) {
+        const uint32_t ri = rec0 + __popc(m_emit & lt);
+        const uint32_t qa = item0 + __popc(m_qa & lt), qb = item0 + n_qa + __popc(m_qb & lt);
+        const uint32_t cap = A.lv[l + 1].cap_items;
+        const bool fits = ri < A.lv[l].cap_recs && (!q_refl || qa < cap) && (!q_refr || qb < cap);
+        if (!fits) {
+          dropped++;
+        } else {
+          double2* R = reinterpret_cast<double2*>(A.lv[l].recs + ri);
+          R[0] = make_double2(stage.d[0][tid], stage.d[1][tid]);
+          R[1] = make_double2(stage.d[2][tid], stage.d[3][tid]);
+          R[2] = make_double2(stage.d[4][tid], stage.d[5][tid]);
+          reinterpret_cast<uint4*>(R)[3] = make_uint4(parent, slot, bits, 0u);
+          if (q_refl) {
+            double2* w = reinterpret_cast<double2*>(A.lv[l + 1].items + qa);
+            w[0] = make_double2(stage.d[6][tid], stage.d[7][tid]);
+            w[1] = make_double2(stage.d[8][tid], stage.d[9][tid]);
+            w[2] = make_double2(stage.d[10][tid], stage.d[11][tid]);
+            reinterpret_cast<uint4*>(w)[3] = make_uint4(ri, 0u, 0u, 0u);
+          }
+          if (q_refr) {
+            double2* w = reinterpret_cast<double2*>(A.lv[l + 1].items + qb);
+            w[0] = make_double2(stage.d[12][tid], stage.d[13][tid]);
+            w[1] = make_double2(stage.d[14][tid], stage.d[15][tid]);
+            w[2] = make_double2(stage.d[16][tid], stage.d[17][tid]);
+            reinterpret_cast<uint4*>(w)[3] = make_uint4(ri, 1u, 0u, 0u);
+          }
+          if (keep) {  // this lane carries on with its first child
+            const int o = has_refl ? 6 : 12;
+            ray.o = v3(stage.d[o][tid], stage.d[o + 1][tid], stage.d[o + 2][tid]);
+            ray.d = v3(stage.d[o + 3][tid], stage.d[o + 4][tid], stage.d[o + 5][tid]);
+            parent = ri;
+            slot = has_refl ? 0u : 1u;
+            active = true;
+          }
         }
       }
+      __syncwarp();
+      if (!keep) break;
     }
-    __syncwarp();
   }
   flush_counters(rc, err, counters);
   if (dropped) atomicAdd(counters + 6, (unsigned long long)dropped);

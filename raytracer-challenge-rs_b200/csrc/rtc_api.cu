@@ -32,8 +32,11 @@ int fail(int code, const std::string& msg) {
   } while (0)
 
 constexpr int N_COUNTERS = 8;
-#ifndef RTK_WAVE_DEFAULT
-#define RTK_WAVE_DEFAULT 0
+#ifndef RTK_WAVE_INLINE_MIN
+#define RTK_WAVE_INLINE_MIN 33
+#endif
+#ifndef RTK_WAVE_MIN_RANKS
+#define RTK_WAVE_MIN_RANKS 3
 #endif
 
 }  // namespace
@@ -57,6 +60,7 @@ struct rtc_scene {
   // the recursive kernel should a queue have overflowed
   char* wave_arena = nullptr;
   size_t wave_bytes = 0;
+  bool has_secondary = false;  // some material reflects or refracts: color_at recurses (world.rs:107-134)
   bool last_wave = false;
   CameraD last_cam{};
   RenderParams last_P{};
@@ -287,26 +291,25 @@ int launch_wave(rtc_scene* s, const CameraD& cam, const RenderParams& P, double*
   uint32_t* n_recs = n_items + 16;
   uint32_t* work = n_items + 32;
   CUDA_TRY(cudaMemsetAsync(base, 0, 256, stream));
-  auto level = [&](int L) {
-    WaveLevel w{};
-    if (L > D) return w;
-    w.items = (WaveItem*)(base + lay[L].items);
-    w.recs = (WaveRec*)(base + lay[L].recs);
-    w.child = (double*)(base + lay[L].child);
-    w.cap_items = lay[L].cap_items;
-    w.cap_recs = lay[L].cap_recs;
-    return w;
-  };
+  WaveArgs A{};
   for (int L = 0; L <= D; L++) {
-    WaveArgs A{};
-    A.cur = level(L);
-    A.next = level(L + 1);
-    A.n_items_cur = n_items + L;
-    A.n_recs_cur = n_recs + L;
-    A.n_items_next = n_items + L + 1;
+    A.lv[L].items = (WaveItem*)(base + lay[L].items);
+    A.lv[L].recs = (WaveRec*)(base + lay[L].recs);
+    A.lv[L].child = (double*)(base + lay[L].child);
+    A.lv[L].cap_items = lay[L].cap_items;
+    A.lv[L].cap_recs = lay[L].cap_recs;
+  }
+  A.n_items = n_items;
+  A.n_recs = n_recs;
+  A.max_depth = D;
+  {
+    static const char* env = std::getenv("RTC_WAVE_INLINE_MIN");
+    A.inline_min = env ? (uint32_t)std::atoi(env) : (uint32_t)RTK_WAVE_INLINE_MIN;
+  }
+  auto level = [&](int L) { return A.lv[L]; };
+  for (int L = 0; L <= D; L++) {
+    A.level = L;
     A.work = work + L;
-    A.parent_child = L > 0 ? level(L - 1).child : nullptr;
-    A.remaining = D - L;
     if (s->has_csg) {
       if (s->big_accel) launch_wave_level<true, 8>(s, cam, P, A, L == 0, out, stream);
       else launch_wave_level<true, RTK_MIN_BLOCKS>(s, cam, P, A, L == 0, out, stream);
@@ -328,20 +331,24 @@ int launch_wave(rtc_scene* s, const CameraD& cam, const RenderParams& P, double*
 
 // RTC_WAVEFRONT=0/1 in the environment overrides the choice (experiments); otherwise RTC_OPT_WAVEFRONT /
 // RTC_OPT_RECURSIVE in rtc_opts.flags, otherwise the measured default.
-bool use_wavefront(const RenderParams& P, bool faithful, uint32_t flags) {
+// Default (measured, profiles/r01g_*): on a whole 1080p frame the recursive kernel is faster (no queue
+// traffic, 2.9 vs 3.3 ms on the glass scene); once the frame is split over >= RTK_WAVE_MIN_RANKS GPUs its
+// serial per-pixel recursion is the critical path (1.16 ms for an eighth of that frame, 0.5 ms as a
+// wavefront). Scenes without reflective or transparent materials never recurse and stay recursive.
+bool use_wavefront(const rtc_scene* s, const RenderParams& P, bool faithful, uint32_t flags) {
   if (faithful || P.aa != 1 || P.average || P.max_depth < 1) return false;
   static const char* env = std::getenv("RTC_WAVEFRONT");
   if (env && env[0] == '0') return false;
   if (env && env[0] == '1') return true;
   if (flags & RTC_OPT_RECURSIVE) return false;
   if (flags & RTC_OPT_WAVEFRONT) return true;
-  return RTK_WAVE_DEFAULT != 0;
+  return s->has_secondary && P.nranks >= RTK_WAVE_MIN_RANKS;
 }
 
 int launch_frame(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool faithful, double* out, cudaStream_t stream) {
   CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, N_COUNTERS * sizeof(unsigned long long), stream));
   CUDA_TRY(cudaEventRecord(s->ev0, stream));
-  s->last_wave = use_wavefront(P, faithful, P.flags);
+  s->last_wave = use_wavefront(s, P, faithful, P.flags);
   int rc;
   if (s->last_wave) {
     s->last_cam = cam; s->last_P = P; s->last_out = out;
@@ -456,6 +463,8 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   rtc_scene* s = new rtc_scene();
   s->device = device;
   s->has_csg = has_csg;
+  for (uint32_t m = 0; m < d->n_materials; m++)
+    if (d->materials[m].reflective != 0.0 || d->materials[m].transparency != 0.0) s->has_secondary = true;
   // 126 MB of L2 on B200: past ~64 MB of nodes + leaf records, traversal is DRAM-latency bound
   s->big_accel = sizeof(BvhNode) * accel.bvh.size() + sizeof(LeafRec) * accel.leaf_recs.size() > ((size_t)64 << 20);
   s->slab_bytes = total;
@@ -631,7 +640,7 @@ int rtc_render(rtc_scene* s, const rtc_camera* camera, const rtc_opts* opts, dou
     cudaPointerAttributes attr;
     // (The wavefront renderer writes a pixel from whichever pass completes it; measured over PCIe that is
     // 9.8 ms against 3.9 ms into a device canvas, so it takes the staged path: device canvas, one DMA.)
-    if (!use_wavefront(P, faithful, P.flags) && cudaPointerGetAttributes(&attr, rgb_host) == cudaSuccess &&
+    if (!use_wavefront(s, P, faithful, P.flags) && cudaPointerGetAttributes(&attr, rgb_host) == cudaSuccess &&
         attr.type == cudaMemoryTypeHost && attr.devicePointer) {
       s->launches = 0;
       rc = launch_frame(s, cam, P, faithful, (double*)attr.devicePointer, s->stream);
