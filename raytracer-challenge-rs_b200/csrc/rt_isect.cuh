@@ -36,7 +36,7 @@ struct SceneView {
   int32_t n_always;
   int32_t n_bvh;             // BVH node count (0: no BVH)
   int32_t n_sph, n_pl;       // always-prefix: [0,n_sph) spheres, [n_sph,n_sph+n_pl) planes, then the rest
-  int32_t _pad;
+  int32_t sane_indices;      // 1: every material's refractive_index is finite and > 0 (schlick() is then finite)
   SphCull sph_cull[SPH_CULL_MAX];  // bounding spheres of the first every-ray spheres (parameter bank)
 };
 

@@ -348,7 +348,7 @@ struct Tracer {
       containers_n1n2(S, neg, cur.node, n1, n2, err);
       next = NX_N1N2;
     }
-    if (next == NX_SHADOW) {  // World::is_shadowed(over_point, light li), world.rs:95-105
+    while (next == NX_SHADOW) {  // World::is_shadowed(over_point, light li), world.rs:95-105
       const rtc_light* L = S.lights + li;
       V3 lp = v3(RTC_LDG(&L->position[0]), RTC_LDG(&L->position[1]), RTC_LDG(&L->position[2]));
       const V3 op = cur.over_point;
@@ -356,8 +356,22 @@ struct Tracer {
       double distance = magnitude(v);
       qray.o = op;
       qray.d = normalize(v);
-      q.init_shadow(distance, err);
       rc.shadow++;
+#if !defined(RTK_NO_BACKFACE_SHADOW_SKIP)
+      // The light is behind the shaded side (material.rs:60, light_dot_normal < 0): lighting() is `ambient`
+      // in shadow and `ambient + 0 + 0` out of it, and `surface` — a sum that starts from +0 and therefore
+      // can never be -0 — takes the same bits from either (x + -0 == x + +0 for every x but -0). The
+      // occlusion query cannot change the frame: the ray is counted (the reference casts it) but not traced.
+      if (dot(qray.d, cur.normalv) < 0.0) {
+        V3 lint = v3(RTC_LDG(&L->intensity[0]), RTC_LDG(&L->intensity[1]), RTC_LDG(&L->intensity[2]));
+        const MatD m = load_material(S, cur.mat);
+        cur.surface = cur.surface + lighting(m, cur.color, qray.d, lint, -cur.ray.d, cur.normalv, true);
+        li++;
+        next = li < S.n_lights ? NX_SHADOW : NX_LIT;
+        continue;
+      }
+#endif
+      q.init_shadow(distance, err);
       phase = PH_SHADOW;
       return false;
     }
@@ -371,7 +385,15 @@ struct Tracer {
       const double reflective = RTC_LDG(&M->reflective), transparency = RTC_LDG(&M->transparency);
       const bool want_reflect = !(feq(reflective, 0.0) || remaining == 0);    // world.rs:108
       const bool want_refract = !(feq(transparency, 0.0) || remaining == 0);  // world.rs:117
-      const bool use_schlick = reflective > 0.0 && transparency > 0.0;        // world.rs:62
+      bool use_schlick = reflective > 0.0 && transparency > 0.0;              // world.rs:62
+      // At remaining == 0 both children are black (world.rs:108,117), so world.rs:64 is
+      // surface + 0·R + 0·(1−R): for any FINITE reflectance R >= 0 that is surface + (+0) + (±0), bit for bit what
+      // the non-Schlick line surface + 0 + 0 gives — and R = schlick() is finite whenever every refractive
+      // index in the scene is finite and positive. Then neither the containers query nor schlick() can
+      // change a bit of the result, and the deepest level (the most populated one on glass) skips both.
+#if !defined(RTK_NO_DEAD_SCHLICK)
+      if (remaining == 0 && S.sane_indices) use_schlick = false;
+#endif
       if (next == NX_LIT && (want_refract || use_schlick)) {
         // n1/n2 are only ever consumed by refracted_color and schlick
         qray = cur.ray;

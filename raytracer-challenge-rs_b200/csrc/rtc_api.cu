@@ -545,6 +545,9 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   v.n_nodes = (int32_t)d->n_nodes;
   v.n_lights = (int32_t)d->n_lights;
   v.has_csg = has_csg ? 1 : 0;
+  v.sane_indices = 1;
+  for (uint32_t m = 0; m < d->n_materials; m++)
+    if (!(d->materials[m].refractive_index > 0.0) || !std::isfinite(d->materials[m].refractive_index)) v.sane_indices = 0;
   *out = s;
   return RTC_OK;
 }

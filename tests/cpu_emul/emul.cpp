@@ -36,7 +36,9 @@ void build_view(const rtc_scene_desc* d, Built& b) {
   v.nodes = d->nodes; v.xforms = d->xforms; v.boxes = d->boxes; v.limits = d->limits;
   v.tri_geom = d->tri_p1e1e2; v.tri_normals = d->tri_normals; v.materials = d->materials;
   v.patterns = d->patterns; v.lights = d->lights; v.csg_parent = b.csg_parent.data();
-  v.n_nodes = n; v.n_lights = (int32_t)d->n_lights; v.has_csg = has_csg ? 1 : 0; v._pad = 0;
+  v.n_nodes = n; v.n_lights = (int32_t)d->n_lights; v.has_csg = has_csg ? 1 : 0; v.sane_indices = 1;
+  for (uint32_t m = 0; m < d->n_materials; m++)
+    if (!(d->materials[m].refractive_index > 0.0) || !std::isfinite(d->materials[m].refractive_index)) v.sane_indices = 0;
   build_accel(d, b.accel);
   v.parent = b.accel.parent.data(); v.prims = b.accel.prims.data(); v.recs = b.accel.recs.data(); v.leaf_recs = b.accel.leaf_recs.data();
   v.bvh = b.accel.bvh.data(); v.n_always = b.accel.n_always; v.n_sph = b.accel.n_sph; v.n_pl = b.accel.n_pl; v.n_bvh = (int32_t)b.accel.bvh.size();
