@@ -348,7 +348,7 @@ struct Tracer {
       containers_n1n2(S, neg, cur.node, n1, n2, err);
       next = NX_N1N2;
     }
-    while (next == NX_SHADOW) {  // World::is_shadowed(over_point, light li), world.rs:95-105
+    if (next == NX_SHADOW) {  // World::is_shadowed(over_point, light li), world.rs:95-105
       const rtc_light* L = S.lights + li;
       V3 lp = v3(RTC_LDG(&L->position[0]), RTC_LDG(&L->position[1]), RTC_LDG(&L->position[2]));
       const V3 op = cur.over_point;
@@ -357,22 +357,23 @@ struct Tracer {
       qray.o = op;
       qray.d = normalize(v);
       rc.shadow++;
+      q.init_shadow(distance, err);
+      phase = PH_SHADOW;
 #if !defined(RTK_NO_BACKFACE_SHADOW_SKIP)
       // The light is behind the shaded side (material.rs:60, light_dot_normal < 0): lighting() is `ambient`
       // in shadow and `ambient + 0 + 0` out of it, and `surface` — a sum that starts from +0 and therefore
       // can never be -0 — takes the same bits from either (x + -0 == x + +0 for every x but -0). The
-      // occlusion query cannot change the frame: the ray is counted (the reference casts it) but not traced.
+      // occlusion query cannot change the frame: the ray is counted (the reference casts it) but the query
+      // is born answered (Q_DONE), so the search returns at once. The lane still spends the shadow phase
+      // with its warp: letting it run ahead desynchronises the warp's phases and costs more in this
+      // function than the skipped search saves (2.61 -> 2.77 ms on the glass scene; skipping ahead only
+      // to a further light helps two-light scenes by 8 % and costs the one-light headline as much, in
+      // both of the forms tried — profiles/r01b_experiment_persistent_refill.md).
       if (dot(qray.d, cur.normalv) < 0.0) {
-        V3 lint = v3(RTC_LDG(&L->intensity[0]), RTC_LDG(&L->intensity[1]), RTC_LDG(&L->intensity[2]));
-        const MatD m = load_material(S, cur.mat);
-        cur.surface = cur.surface + lighting(m, cur.color, qray.d, lint, -cur.ray.d, cur.normalv, true);
-        li++;
-        next = li < S.n_lights ? NX_SHADOW : NX_LIT;
-        continue;
+        q.mode = Q_DONE;
+        q.node = 1;
       }
 #endif
-      q.init_shadow(distance, err);
-      phase = PH_SHADOW;
       return false;
     }
     bool descend = false;
