@@ -21,8 +21,8 @@
 //
 // Every arithmetic expression and its order per call is the recursive kernel's, so the frame is
 // bit-identical (tests/test_gpu_parity.py::test_wavefront_*). All launches are persistent grids
-// (SMs x resident CTAs, grid-stride over a device-side count) queued back to back on one stream: no
-// host round trip between levels. Queue capacity is optimistic (2 items per pixel and level, the
+// (SMs x resident CTAs, 32 items per warp from a device-side counter) queued back to back on one stream:
+// no host round trip between levels. Queue capacity is optimistic (2 items per pixel and level, the
 // worst case is 2^L); an overflow raises a flag and rtc_scene_finish re-renders the frame with the
 // recursive kernel.
 #pragma once
@@ -60,8 +60,7 @@ struct WaveArgs {
   uint32_t* work;         // per pass: items handed out so far
   int32_t level;          // the level whose queue this pass drains
   int32_t max_depth;
-  uint32_t inline_min;    // keep the first child in-lane when at least this many lanes of the warp emit (33: never)
-  uint32_t _pad;
+  uint32_t _pad[2];
 };
 
 // counters[6]: items dropped because a queue was full (→ the host re-renders with the recursive kernel)
@@ -69,160 +68,150 @@ __device__ __forceinline__ void wave_store_color(double* dst, V3 c) {
   dst[0] = c.x; dst[1] = c.y; dst[2] = c.z;
 }
 
-// Per-thread staging of an emitted call in SHARED memory (field-major, so lane-consecutive = bank-
-// consecutive): the suspended shade_hit and both child rays leave the register file the moment
-// Tracer::advance produces them, and come back after the warp has agreed on queue slots.
-constexpr int WAVE_STAGE_DOUBLES = 18;  // surface 3, reflective, transparency, reflectance, reflection ray 6, refraction ray 6
-struct WaveStage {
-  double d[WAVE_STAGE_DOUBLES][128];
-  uint32_t bits[128];
-};
-
 // One forward pass over the queue of level A.level. PRIMARY: items are the pixels of this rank's tiles, a
 // warp = one 8x4 patch. Work is handed out 32 items at a time from a device counter (patches / queue
 // slices differ in cost by more than 10x; a static split leaves the chip waiting for the unluckiest warp).
 //
-// A call that needs children may KEEP one of them: the lane stores its WaveRec and carries on with the
-// reflection ray (the refraction ray when there is no reflection) as a call of the next level, in the
-// same pass — no queue round trip for mirror chains; only the second child of a glass hit is queued.
-// A thread's serial chain is then at most max_depth + 1 calls, against 2^(max_depth+1) - 1 recursively.
-// All lanes of a warp move down one level per step, so the level is warp-uniform. Keeping pays while
-// most of the warp carries on (A.inline_min); a sparse warp queues everything instead.
+// A call that needs children reserves its WaveRec and queue slots the moment Tracer::advance produces
+// them, straight from registers: the lanes that reach the emission together (__activemask) elect a
+// leader, which does ONE atomicAdd per counter for the group (per-lane atomics on one address serialise
+// in a single L2 slice: 6.0 ms instead of 3.9), and every lane writes its 64-byte record and its
+// children's 64-byte items with 16-byte stores. No shared memory: L1 keeps its full size.
 template <bool HAS_CSG, bool PRIMARY, int MINB>
 __global__ void __launch_bounds__(128, MINB) wave_forward_kernel(SceneView S, CameraD cam, RenderParams P, WaveArgs A,
                                                                  double* __restrict__ canvas,
                                                                  unsigned long long* __restrict__ counters) {
-  __shared__ WaveStage stage;
   // a queue overflowed in an earlier pass: the frame is going to be re-rendered, and the queues have holes
   if (!PRIMARY && *reinterpret_cast<const volatile unsigned long long*>(counters + 6) != 0ull) return;
-  const uint32_t lane = threadIdx.x & 31u, tid = threadIdx.x;
+  const uint32_t lane = threadIdx.x & 31u;
   Scratch<HAS_CSG> scratch;
   RayCounters rc = {0u, 0u, 0u, 0u};
   uint32_t err = 0, dropped = 0;
+  const int l = PRIMARY ? 0 : A.level;
   // patches: 8 px wide, 4 rows tall over the owned-row domain
   const uint32_t pw = (cam.hsize + 7u) >> 3, ph = (P.owned_rows + 3u) >> 2;
-  const uint32_t n = PRIMARY ? pw * ph * 32u : min(A.n_items[A.level], A.lv[A.level].cap_items);
-  // the next batch's index is requested before the current batch is processed: the atomic's round trip
-  // to L2 overlaps the work instead of preceding it
+  const uint32_t n = PRIMARY ? pw * ph * 32u : min(A.n_items[l], A.lv[l].cap_items);
+  uint32_t parent = 0, slot = 0;
+  // item idx of this pass → this lane's ray / parent / slot; false: nothing to trace (pixel outside the frame)
+  auto load_item = [&](uint32_t idx, RayD& ray) -> bool {
+    if (PRIMARY) {
+      const uint32_t patch = idx >> 5, li = idx & 31u;
+      const uint32_t px = (patch % pw) * 8u + (li & 7u), oy = (patch / pw) * 4u + (li >> 3);
+      const uint32_t k = oy / P.tile_rows, r = oy - k * P.tile_rows;
+      const uint32_t py = (P.rank + k * P.nranks) * P.tile_rows + r;
+      if (!(px < cam.hsize && oy < P.owned_rows && py >= P.row_begin && py < P.row_end)) return false;
+      rc.primary++;
+      ray = ray_for_pixel(cam, px, py, 0.5, 0.5);
+      parent = py * cam.hsize + px;  // Canvas::pixel_idx, canvas.rs:44-48
+    } else {
+      const double2* q = reinterpret_cast<const double2*>(A.lv[l].items + idx);
+      const double2 a = __ldcs(q), b = __ldcs(q + 1), c = __ldcs(q + 2);
+      const int4 h = __ldcs(reinterpret_cast<const int4*>(q + 3));
+      ray.o = v3(a.x, a.y, b.x); ray.d = v3(b.y, c.x, c.y);
+      parent = (uint32_t)h.x; slot = (uint32_t)h.y;
+    }
+    return true;
+  };
+  // Tracer::advance<WAVE> hands a call that needs children here (divergent code: only the lanes that
+  // emit in this very advance() are converged at this point)
+  auto put = [&](const Frame& f, const RayD& refl, bool has_reflect) {
+    const bool has_refr = (f.bits & FR_NEED_REFRACT) != 0;
+    const unsigned m = __activemask();
+    const unsigned m_refl = __ballot_sync(m, has_reflect), m_refr = __ballot_sync(m, has_refr);
+    const int leader = __ffs(m) - 1;
+    uint32_t rec0 = 0, item0 = 0;
+    if ((int)lane == leader) {
+      rec0 = atomicAdd(A.n_recs + l, (uint32_t)__popc(m));
+      item0 = atomicAdd(A.n_items + l + 1, (uint32_t)(__popc(m_refl) + __popc(m_refr)));
+    }
+    rec0 = __shfl_sync(m, rec0, leader);
+    item0 = __shfl_sync(m, item0, leader);
+    const uint32_t lt = (1u << lane) - 1u;
+    const uint32_t ri = rec0 + __popc(m & lt);
+    const uint32_t i_refl = item0 + __popc(m_refl & lt), i_refr = item0 + __popc(m_refl) + __popc(m_refr & lt);
+    const uint32_t cap = A.lv[l + 1].cap_items;
+    if (ri >= A.lv[l].cap_recs || (has_reflect && i_refl >= cap) || (has_refr && i_refr >= cap)) { dropped++; return; }
+    double2* R = reinterpret_cast<double2*>(A.lv[l].recs + ri);
+    R[0] = make_double2(f.surface.x, f.surface.y);
+    R[1] = make_double2(f.surface.z, f.reflective);
+    R[2] = make_double2(f.transparency, f.reflectance);
+    reinterpret_cast<uint4*>(R)[3] = make_uint4(parent, slot, f.bits | (has_reflect ? WR_HAS_REFLECT : 0u), 0u);
+    if (has_reflect) {
+      double2* w = reinterpret_cast<double2*>(A.lv[l + 1].items + i_refl);
+      w[0] = make_double2(refl.o.x, refl.o.y);
+      w[1] = make_double2(refl.o.z, refl.d.x);
+      w[2] = make_double2(refl.d.y, refl.d.z);
+      reinterpret_cast<uint4*>(w)[3] = make_uint4(ri, 0u, 0u, 0u);
+    }
+    if (has_refr) {
+      double2* w = reinterpret_cast<double2*>(A.lv[l + 1].items + i_refr);
+      w[0] = make_double2(f.refr_ray.o.x, f.refr_ray.o.y);
+      w[1] = make_double2(f.refr_ray.o.z, f.refr_ray.d.x);
+      w[2] = make_double2(f.refr_ray.d.y, f.refr_ray.d.z);
+      reinterpret_cast<uint4*>(w)[3] = make_uint4(ri, 1u, 0u, 0u);
+    }
+  };
+  auto deliver = [&](V3 c) {
+    double* dst = l == 0 ? canvas + (size_t)parent * 3 : A.lv[l - 1].child + ((size_t)parent * 2 + slot) * 3;
+    wave_store_color(dst, c);
+  };
+  Tracer tr;
+  RayD ray;
+  ray.o = ray.d = v3(0.0, 0.0, 0.0);
+#if defined(RTK_WAVE_REFILL)
+  // Lane-level streams: a lane that has finished its call takes the next item at the top of the very next
+  // turn (the lanes that are idle together fetch together: one atomicAdd per group), so the warp keeps
+  // meeting at the one search site with most lanes busy, in whatever phase of whatever call each is.
+  bool busy = false, drained = false;
+  for (;;) {
+    if (!busy && !drained) {
+      const unsigned m = __activemask();
+      const int leader = __ffs(m) - 1;
+      uint32_t base = 0;
+      if ((int)lane == leader) base = atomicAdd(A.work, (uint32_t)__popc(m));
+      base = __shfl_sync(m, base, leader);
+      const uint32_t idx = base + __popc(m & ((1u << lane) - 1u));
+      if (idx >= n) {
+        drained = true;
+      } else if (load_item(idx, ray)) {
+        tr.start(ray, A.max_depth - l, nullptr, &err);
+        busy = true;
+      }
+    }
+    __syncwarp();
+    if (!__any_sync(0xffffffffu, busy)) {
+      if (__all_sync(0xffffffffu, drained)) break;
+      continue;
+    }
+    if (busy) {
+      search<HAS_CSG, false>(S, tr.qray, tr.q, scratch.csg(), &scratch.bvh, &err);
+      if (tr.template advance<true>(S, nullptr, scratch.neg, rc, &err, put)) {
+        if (!tr.w_emit) deliver(tr.result);
+        busy = false;
+      }
+    }
+    __syncwarp();
+  }
+#else
+  // Warp batches of 32 consecutive items. The next batch's index is requested before the current batch
+  // is processed: the atomic's round trip to L2 overlaps the work instead of preceding it.
   uint32_t next = 0;
   if (lane == 0) next = atomicAdd(A.work, 32u);
   for (;;) {
     const uint32_t base = __shfl_sync(0xffffffffu, next, 0);
     if (base >= n) break;
     if (lane == 0) next = atomicAdd(A.work, 32u);
-    const uint32_t idx = base + lane;
-    bool active = idx < n;
-    RayD ray;
-    ray.o = ray.d = v3(0.0, 0.0, 0.0);
-    uint32_t parent = 0, slot = 0;
-    if (PRIMARY) {
-      const uint32_t patch = base >> 5;
-      const uint32_t px = (patch % pw) * 8u + (lane & 7u), oy = (patch / pw) * 4u + (lane >> 3);
-      const uint32_t k = oy / P.tile_rows, r = oy - k * P.tile_rows;
-      const uint32_t py = (P.rank + k * P.nranks) * P.tile_rows + r;
-      active = px < cam.hsize && oy < P.owned_rows && py >= P.row_begin && py < P.row_end;
-      if (active) {
-        rc.primary++;
-        ray = ray_for_pixel(cam, px, py, 0.5, 0.5);
-        parent = py * cam.hsize + px;  // Canvas::pixel_idx, canvas.rs:44-48
+    if (base + lane < n && load_item(base + lane, ray)) {
+      tr.start(ray, A.max_depth - l, nullptr, &err);
+      for (;;) {
+        search<HAS_CSG, false>(S, tr.qray, tr.q, scratch.csg(), &scratch.bvh, &err);
+        if (tr.template advance<true>(S, nullptr, scratch.neg, rc, &err, put)) break;
       }
-    } else if (active) {
-      const WaveItem* it = A.lv[A.level].items + idx;
-      const double2* q = reinterpret_cast<const double2*>(it);
-      const double2 a = __ldcs(q), b = __ldcs(q + 1), c = __ldcs(q + 2);
-      const int4 h = __ldcs(reinterpret_cast<const int4*>(q + 3));
-      ray.o = v3(a.x, a.y, b.x); ray.d = v3(b.y, c.x, c.y);
-      parent = (uint32_t)h.x; slot = (uint32_t)h.y;
+      if (!tr.w_emit) deliver(tr.result);
     }
-    for (int l = PRIMARY ? 0 : A.level;; l++) {  // the chain of kept children; l is warp-uniform
-      bool emit = false;
-      V3 result = v3(0.0, 0.0, 0.0);
-      if (active) {
-        Tracer tr;
-        tr.start(ray, A.max_depth - l, nullptr, &err);
-        auto put = [&](const Frame& f, const RayD& refl, bool has_reflect) {
-          stage.d[0][tid] = f.surface.x; stage.d[1][tid] = f.surface.y; stage.d[2][tid] = f.surface.z;
-          stage.d[3][tid] = f.reflective; stage.d[4][tid] = f.transparency; stage.d[5][tid] = f.reflectance;
-          stage.d[6][tid] = refl.o.x; stage.d[7][tid] = refl.o.y; stage.d[8][tid] = refl.o.z;
-          stage.d[9][tid] = refl.d.x; stage.d[10][tid] = refl.d.y; stage.d[11][tid] = refl.d.z;
-          stage.d[12][tid] = f.refr_ray.o.x; stage.d[13][tid] = f.refr_ray.o.y; stage.d[14][tid] = f.refr_ray.o.z;
-          stage.d[15][tid] = f.refr_ray.d.x; stage.d[16][tid] = f.refr_ray.d.y; stage.d[17][tid] = f.refr_ray.d.z;
-          stage.bits[tid] = f.bits | (has_reflect ? WR_HAS_REFLECT : 0u);
-        };
-        for (;;) {
-          search<HAS_CSG, false>(S, tr.qray, tr.q, scratch.csg(), &scratch.bvh, &err);
-          if (tr.template advance<true>(S, nullptr, scratch.neg, rc, &err, put)) break;
-        }
-        emit = tr.w_emit;
-        result = tr.result;
-      }
-      __syncwarp();
-      if (active && !emit) {
-        double* dst = l == 0 ? canvas + (size_t)parent * 3 : A.lv[l - 1].child + ((size_t)parent * 2 + slot) * 3;
-        wave_store_color(dst, result);
-      }
-      // warp-aggregated allocation: one record per emitting lane and a queue slot per queued child. The
-      // first child is KEPT (the lane carries on with it) only if at least A.inline_min lanes emit: a
-      // mostly idle warp is better off handing everything to the queue, where the next pass packs it.
-      const uint32_t m_emit = __ballot_sync(0xffffffffu, emit);
-      if (m_emit == 0u) break;
-      const bool keep = (uint32_t)__popc(m_emit) >= A.inline_min;
-      const uint32_t bits = emit ? stage.bits[tid] : 0u;
-      const bool has_refl = (bits & WR_HAS_REFLECT) != 0, has_refr = (bits & FR_NEED_REFRACT) != 0;
-      // queued: (reflection unless kept) and (refraction unless it is the kept first child)
-      const bool q_refl = has_refl && !keep, q_refr = has_refr && (has_refl || !keep);
-      const uint32_t m_qa = __ballot_sync(0xffffffffu, q_refl), m_qb = __ballot_sync(0xffffffffu, q_refr);
-      const uint32_t n_qa = __popc(m_qa);
-      uint32_t rec0 = 0, item0 = 0;
-      if (lane == 0) {
-        rec0 = atomicAdd(A.n_recs + l, (uint32_t)__popc(m_emit));
-        if (m_qa | m_qb) item0 = atomicAdd(A.n_items + l + 1, n_qa + (uint32_t)__popc(m_qb));
-      }
-      rec0 = __shfl_sync(0xffffffffu, rec0, 0);
-      item0 = __shfl_sync(0xffffffffu, item0, 0);
-      const uint32_t lt = (1u << lane) - 1u;
-      active = false;
-      if (emit) {
-        const uint32_t ri = rec0 + __popc(m_emit & lt);
-        const uint32_t qa = item0 + __popc(m_qa & lt), qb = item0 + n_qa + __popc(m_qb & lt);
-        const uint32_t cap = A.lv[l + 1].cap_items;
-        const bool fits = ri < A.lv[l].cap_recs && (!q_refl || qa < cap) && (!q_refr || qb < cap);
-        if (!fits) {
-          dropped++;
-        } else {
-          double2* R = reinterpret_cast<double2*>(A.lv[l].recs + ri);
-          R[0] = make_double2(stage.d[0][tid], stage.d[1][tid]);
-          R[1] = make_double2(stage.d[2][tid], stage.d[3][tid]);
-          R[2] = make_double2(stage.d[4][tid], stage.d[5][tid]);
-          reinterpret_cast<uint4*>(R)[3] = make_uint4(parent, slot, bits, 0u);
-          if (q_refl) {
-            double2* w = reinterpret_cast<double2*>(A.lv[l + 1].items + qa);
-            w[0] = make_double2(stage.d[6][tid], stage.d[7][tid]);
-            w[1] = make_double2(stage.d[8][tid], stage.d[9][tid]);
-            w[2] = make_double2(stage.d[10][tid], stage.d[11][tid]);
-            reinterpret_cast<uint4*>(w)[3] = make_uint4(ri, 0u, 0u, 0u);
-          }
-          if (q_refr) {
-            double2* w = reinterpret_cast<double2*>(A.lv[l + 1].items + qb);
-            w[0] = make_double2(stage.d[12][tid], stage.d[13][tid]);
-            w[1] = make_double2(stage.d[14][tid], stage.d[15][tid]);
-            w[2] = make_double2(stage.d[16][tid], stage.d[17][tid]);
-            reinterpret_cast<uint4*>(w)[3] = make_uint4(ri, 1u, 0u, 0u);
-          }
-          if (keep) {  // this lane carries on with its first child
-            const int o = has_refl ? 6 : 12;
-            ray.o = v3(stage.d[o][tid], stage.d[o + 1][tid], stage.d[o + 2][tid]);
-            ray.d = v3(stage.d[o + 3][tid], stage.d[o + 4][tid], stage.d[o + 5][tid]);
-            parent = ri;
-            slot = has_refl ? 0u : 1u;
-            active = true;
-          }
-        }
-      }
-      __syncwarp();
-      if (!keep) break;
-    }
+    __syncwarp();
   }
+#endif
   flush_counters(rc, err, counters);
   if (dropped) atomicAdd(counters + 6, (unsigned long long)dropped);
 }

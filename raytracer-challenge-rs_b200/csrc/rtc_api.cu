@@ -32,9 +32,6 @@ int fail(int code, const std::string& msg) {
   } while (0)
 
 constexpr int N_COUNTERS = 8;
-#ifndef RTK_WAVE_INLINE_MIN
-#define RTK_WAVE_INLINE_MIN 33
-#endif
 #ifndef RTK_WAVE_MIN_RANKS
 #define RTK_WAVE_MIN_RANKS 3
 #endif
@@ -302,10 +299,6 @@ int launch_wave(rtc_scene* s, const CameraD& cam, const RenderParams& P, double*
   A.n_items = n_items;
   A.n_recs = n_recs;
   A.max_depth = D;
-  {
-    static const char* env = std::getenv("RTC_WAVE_INLINE_MIN");
-    A.inline_min = env ? (uint32_t)std::atoi(env) : (uint32_t)RTK_WAVE_INLINE_MIN;
-  }
   auto level = [&](int L) { return A.lv[L]; };
   for (int L = 0; L <= D; L++) {
     A.level = L;
