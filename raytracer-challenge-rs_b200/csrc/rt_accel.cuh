@@ -133,10 +133,13 @@ RTC_HD bool quot_unwanted(const Query& C, double num, double den) {
 // World::intersect → query. FAITHFUL: the reference's own search order, node by node (walk_range
 // over the whole array). Otherwise: the prims tested for every ray, then the BVH; ONE leaf-test
 // site and ONE candidate site serve both, so the hot loop stays small.
-template <bool HAS_CSG, bool FAITHFUL>
+// LEAN (FAITHFUL == 2): the scene is every-ray spheres and planes only (no BVH, no other kinds, no CSG) —
+// the host picks this instantiation so that the generic leaf tests and the traversal are not even in
+// the kernel: the hot code of the glass and chapter-7 scenes then fits the instruction caches better.
+template <bool HAS_CSG, int FAITHFUL>
 RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs, BvhStack* st, uint32_t* err) {
   RTK_COUNT(walks, 1);
-  if constexpr (FAITHFUL) {
+  if constexpr (FAITHFUL == 1) {
     (void)st;
     walk_range<HAS_CSG>(S, ray, C, cs, err, 0, S.n_nodes);
     return;
@@ -229,6 +232,7 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
       if (quot_unwanted(C, -oy, dy)) continue;
       cand(-oy / dy, i, flags, par);
     }
+    if constexpr (FAITHFUL == 2) { (void)st; (void)cs; return; }
     // ---- the remaining every-ray prims, then the BVH ---------------------------------------------------
     // "while-while" traversal: every lane first walks inner nodes until it holds a leaf (or runs out),
     // and only then does the warp test leaf prims — so the (long) leaf code runs with as many lanes as

@@ -55,7 +55,7 @@ __device__ __forceinline__ void flush_counters(const RayCounters& rc, uint32_t e
 // shading just fits) for scenes whose tables live in L1/L2; 8 (64 registers, 32 warps per SM) for BVHs
 // far larger than L2, where traversal waits on DRAM and only more warps hide it (1 M triangles at 4K:
 // 91 → 69 ms; an 8 k-triangle mesh is 25 % slower that way, so the host picks by accelerator size).
-template <bool HAS_CSG, bool FAITHFUL, int MINB = RTK_MIN_BLOCKS>
+template <bool HAS_CSG, int FAITHFUL, int MINB = RTK_MIN_BLOCKS>
 __global__ void __launch_bounds__(128, MINB) render_kernel(SceneView S, CameraD cam, RenderParams P, double* __restrict__ out,
                                                                      unsigned long long* __restrict__ counters) {
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;

@@ -487,7 +487,7 @@ struct Tracer {
   }
 };
 
-template <bool HAS_CSG, bool FAITHFUL>
+template <bool HAS_CSG, int FAITHFUL>
 RTC_HD V3 color_at(const SceneView& S, const RayD& ray, int max_depth, Scratch<HAS_CSG>& scratch, RayCounters& rc,
                    uint32_t* err, double* t_out = nullptr) {
   Tracer tr;
@@ -542,7 +542,7 @@ RTC_HD void aa_offset(uint32_t aa, uint32_t s, double& ox, double& oy) {
 
 // One pixel of Camera::render (aa==1, camera.rs:133-148: colour stored as is) or of
 // render_multithreaded (camera.rs:178-187: Color::average = sequential sum * (1.0/n)).
-template <bool HAS_CSG, bool FAITHFUL>
+template <bool HAS_CSG, int FAITHFUL>
 RTC_HD V3 render_pixel(const SceneView& S, const CameraD& cam, uint32_t px, uint32_t py, uint32_t aa, bool average,
                        int max_depth, Scratch<HAS_CSG>& scratch, RayCounters& rc, uint32_t* err) {
   // ONE color_at site for both (two would double the kernel's code and thrash the instruction cache)

@@ -77,7 +77,7 @@ __device__ __forceinline__ void wave_store_color(double* dst, V3 c) {
 // leader, which does ONE atomicAdd per counter for the group (per-lane atomics on one address serialise
 // in a single L2 slice: 6.0 ms instead of 3.9), and every lane writes its 64-byte record and its
 // children's 64-byte items with 16-byte stores. No shared memory: L1 keeps its full size.
-template <bool HAS_CSG, bool PRIMARY, int MINB>
+template <bool HAS_CSG, bool PRIMARY, int MINB, int MODE = 0>
 __global__ void __launch_bounds__(128, MINB) wave_forward_kernel(SceneView S, CameraD cam, RenderParams P, WaveArgs A,
                                                                  double* __restrict__ canvas,
                                                                  unsigned long long* __restrict__ counters) {
@@ -184,7 +184,7 @@ __global__ void __launch_bounds__(128, MINB) wave_forward_kernel(SceneView S, Ca
       continue;
     }
     if (busy) {
-      search<HAS_CSG, false>(S, tr.qray, tr.q, scratch.csg(), &scratch.bvh, &err);
+      search<HAS_CSG, MODE>(S, tr.qray, tr.q, scratch.csg(), &scratch.bvh, &err);
       if (tr.template advance<true>(S, nullptr, scratch.neg, rc, &err, put)) {
         if (!tr.w_emit) deliver(tr.result);
         busy = false;
@@ -204,7 +204,7 @@ __global__ void __launch_bounds__(128, MINB) wave_forward_kernel(SceneView S, Ca
     if (base + lane < n && load_item(base + lane, ray)) {
       tr.start(ray, A.max_depth - l, nullptr, &err);
       for (;;) {
-        search<HAS_CSG, false>(S, tr.qray, tr.q, scratch.csg(), &scratch.bvh, &err);
+        search<HAS_CSG, MODE>(S, tr.qray, tr.q, scratch.csg(), &scratch.bvh, &err);
         if (tr.template advance<true>(S, nullptr, scratch.neg, rc, &err, put)) break;
       }
       if (!tr.w_emit) deliver(tr.result);

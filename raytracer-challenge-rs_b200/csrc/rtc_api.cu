@@ -57,6 +57,7 @@ struct rtc_scene {
   // the recursive kernel should a queue have overflowed
   char* wave_arena = nullptr;
   size_t wave_bytes = 0;
+  bool lean = false;           // every-ray spheres and planes only: the kernels without BVH / generic leaf code
   bool has_secondary = false;  // some material reflects or refracts: color_at recurses (world.rs:107-134)
   bool last_wave = false;
   CameraD last_cam{};
@@ -198,6 +199,8 @@ int launch_rows(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool fa
       if (faithful) render_kernel<true, true><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
       else if (s->big_accel) render_kernel<true, false, 8><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
       else render_kernel<true, false><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
+    } else if (s->lean && !faithful) {
+      render_kernel<false, 2><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
     } else {
       if (faithful) render_kernel<false, true><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
       else if (s->big_accel) render_kernel<false, false, 8><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
@@ -254,12 +257,12 @@ int ensure_arena(rtc_scene* s, size_t need) {
   return RTC_OK;
 }
 
-template <bool HAS_CSG, int MINB>
+template <bool HAS_CSG, int MINB, int MODE = 0>
 void launch_wave_level(rtc_scene* s, const CameraD& cam, const RenderParams& P, const WaveArgs& A, bool primary, double* out,
                        cudaStream_t stream) {
   const int grid = s->sm_count * MINB;
-  if (primary) wave_forward_kernel<HAS_CSG, true, MINB><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
-  else wave_forward_kernel<HAS_CSG, false, MINB><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+  if (primary) wave_forward_kernel<HAS_CSG, true, MINB, MODE><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+  else wave_forward_kernel<HAS_CSG, false, MINB, MODE><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
   s->launches++;
 }
 
@@ -306,6 +309,8 @@ int launch_wave(rtc_scene* s, const CameraD& cam, const RenderParams& P, double*
     if (s->has_csg) {
       if (s->big_accel) launch_wave_level<true, 8>(s, cam, P, A, L == 0, out, stream);
       else launch_wave_level<true, RTK_MIN_BLOCKS>(s, cam, P, A, L == 0, out, stream);
+    } else if (s->lean) {
+      launch_wave_level<false, RTK_MIN_BLOCKS, 2>(s, cam, P, A, L == 0, out, stream);
     } else {
       if (s->big_accel) launch_wave_level<false, 8>(s, cam, P, A, L == 0, out, stream);
       else launch_wave_level<false, RTK_MIN_BLOCKS>(s, cam, P, A, L == 0, out, stream);
@@ -538,6 +543,7 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   v.n_nodes = (int32_t)d->n_nodes;
   v.n_lights = (int32_t)d->n_lights;
   v.has_csg = has_csg ? 1 : 0;
+  s->lean = !has_csg && accel.bvh.empty() && accel.n_always == accel.n_sph + accel.n_pl;
   v.sane_indices = 1;
   for (uint32_t m = 0; m < d->n_materials; m++)
     if (!(d->materials[m].refractive_index > 0.0) || !std::isfinite(d->materials[m].refractive_index)) v.sane_indices = 0;
