@@ -233,6 +233,9 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
       cand(-oy / dy, i, flags, par);
     }
     if constexpr (FAITHFUL == 2) { (void)st; (void)cs; return; }
+    // FAITHFUL == 4: no cube / cylinder / cone / CSG anywhere (every-ray prims are spheres and planes, BVH prims
+    // are triangles and spheres): the generic leaf test is not in the kernel
+    constexpr bool NO_GENERIC = FAITHFUL == 4;
     // ---- the remaining every-ray prims, then the BVH ---------------------------------------------------
     // "while-while" traversal: every lane first walks inner nodes until it holds a leaf (or runs out),
     // and only then does the warp test leaf prims — so the (long) leaf code runs with as many lanes as
@@ -250,7 +253,7 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
         LeafHits hits;
         bool generic = false;
         RTK_COUNT(prim_tests, 1);
-        if (k < S.n_always) {  // (uniform per run) every-ray prim: one 128-byte record
+        if (!NO_GENERIC && k < S.n_always) {  // (uniform per run) every-ray prim: one 128-byte record
           const PrimRec* rec = S.recs + k;
 #if defined(__CUDA_ARCH__)
           const int4 hd = __ldg(reinterpret_cast<const int4*>(rec));
@@ -297,12 +300,12 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
           } else if (nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE) {
             double t, u, v;
             if (isect_triangle(lr, lrec->g, t, u, v)) hits.push(t);
-          } else {  // cube, bounded cylinder
+          } else if (!NO_GENERIC) {  // cube, bounded cylinder
             nd.aux = RTC_LDG(&lrec->aux);
             generic = true;
           }
         }
-        if (generic) {  // ONE isect_leaf site for every-ray prims and the BVH's non-triangle kinds
+        if (!NO_GENERIC && generic) {  // ONE isect_leaf site for every-ray prims and the BVH's non-triangle kinds
           LeafHits h;
           isect_leaf(S, nd, lr, h);
           hits = h;

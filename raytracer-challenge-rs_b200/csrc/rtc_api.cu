@@ -58,6 +58,7 @@ struct rtc_scene {
   char* wave_arena = nullptr;
   size_t wave_bytes = 0;
   bool lean = false;           // every-ray spheres and planes only: the kernels without BVH / generic leaf code
+  bool tri_sph_only = false;   // spheres/planes every ray + a BVH of triangles and spheres: no generic leaf code
   bool has_secondary = false;  // some material reflects or refracts: color_at recurses (world.rs:107-134)
   bool last_wave = false;
   CameraD last_cam{};
@@ -201,6 +202,9 @@ int launch_rows(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool fa
       else render_kernel<true, false><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
     } else if (s->lean && !faithful) {
       render_kernel<false, 2><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
+    } else if (s->tri_sph_only && !faithful) {
+      if (s->big_accel) render_kernel<false, 4, 8><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
+      else render_kernel<false, 4><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
     } else {
       if (faithful) render_kernel<false, true><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
       else if (s->big_accel) render_kernel<false, false, 8><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
@@ -311,6 +315,9 @@ int launch_wave(rtc_scene* s, const CameraD& cam, const RenderParams& P, double*
       else launch_wave_level<true, RTK_MIN_BLOCKS>(s, cam, P, A, L == 0, out, stream);
     } else if (s->lean) {
       launch_wave_level<false, RTK_MIN_BLOCKS, 2>(s, cam, P, A, L == 0, out, stream);
+    } else if (s->tri_sph_only) {
+      if (s->big_accel) launch_wave_level<false, 8, 4>(s, cam, P, A, L == 0, out, stream);
+      else launch_wave_level<false, RTK_MIN_BLOCKS, 4>(s, cam, P, A, L == 0, out, stream);
     } else {
       if (s->big_accel) launch_wave_level<false, 8>(s, cam, P, A, L == 0, out, stream);
       else launch_wave_level<false, RTK_MIN_BLOCKS>(s, cam, P, A, L == 0, out, stream);
@@ -544,6 +551,11 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   v.n_lights = (int32_t)d->n_lights;
   v.has_csg = has_csg ? 1 : 0;
   s->lean = !has_csg && accel.bvh.empty() && accel.n_always == accel.n_sph + accel.n_pl;
+  s->tri_sph_only = !has_csg && !accel.bvh.empty() && accel.n_always == accel.n_sph + accel.n_pl;
+  for (const LeafRec& lr : accel.leaf_recs) {
+    const uint32_t k = lr.kind_flags >> 24;
+    if (k != RTC_SPHERE && k != RTC_TRIANGLE && k != RTC_SMOOTH_TRIANGLE) { s->tri_sph_only = false; break; }
+  }
   v.sane_indices = 1;
   for (uint32_t m = 0; m < d->n_materials; m++)
     if (!(d->materials[m].refractive_index > 0.0) || !std::isfinite(d->materials[m].refractive_index)) v.sane_indices = 0;
