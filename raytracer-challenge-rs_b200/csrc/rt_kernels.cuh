@@ -46,6 +46,40 @@ __device__ __forceinline__ void flush_counters(const RayCounters& rc, uint32_t e
   }
 }
 
+// A warp's 8x4 patch is four row segments of 8 pixels = 24 doubles = 192 contiguous bytes. Storing c.x, c.y,
+// c.z per lane is three instructions of 8-byte pieces at a 24-byte stride: every 32-byte sector is written three
+// times in part, which a device canvas absorbs in L2 but a mapped HOST canvas (PCIe) or a PEER canvas (NVLink) pays
+// for per piece — at 2.05 ms per frame the link's small-write rate stretched the kernel to 3.3 ms. Here the 8 lanes
+// of a row transpose through shuffles so that one instruction writes 128 contiguous bytes (16 B per lane) and a
+// second the remaining 64. Needs the whole warp (full patch) and a 16-byte aligned segment; otherwise plain stores.
+// Called by all 32 lanes of the warp, converged (`alive`: this lane has a pixel).
+__device__ __forceinline__ void store_patch_row(double* o, V3 c, uint32_t lane, bool alive) {
+#if defined(RTK_PLAIN_STORES)
+  if (alive) { o[0] = c.x; o[1] = c.y; o[2] = c.z; }
+  return;
+#endif
+  const uint32_t j = lane & 7u;
+  const bool ok = alive && ((reinterpret_cast<uintptr_t>(o - 3 * j)) & 15u) == 0;
+  if (!__all_sync(0xffffffffu, ok)) {
+    if (alive) { o[0] = c.x; o[1] = c.y; o[2] = c.z; }
+    return;
+  }
+  // value k (0..23) of the segment lives in lane k/3, component k%3
+  auto value = [&](uint32_t k) {
+    const int src = (int)(k / 3u);
+    const uint32_t m = k - 3u * (uint32_t)src;
+    const double x = __shfl_sync(0xffffffffu, c.x, src, 8), y = __shfl_sync(0xffffffffu, c.y, src, 8),
+                 z = __shfl_sync(0xffffffffu, c.z, src, 8);
+    return m == 0u ? x : (m == 1u ? y : z);
+  };
+  double* seg = o - 3 * j;
+  const double a0 = value(2u * j), a1 = value(2u * j + 1u);
+  const uint32_t kb = 16u + 2u * (j & 3u);
+  const double b0 = value(kb), b1 = value(kb + 1u);
+  reinterpret_cast<double2*>(seg)[j] = make_double2(a0, a1);
+  if (j < 4u) reinterpret_cast<double2*>(seg)[8u + j] = make_double2(b0, b1);
+}
+
 // Camera::render / render_multithreaded: one thread per pixel (all its AA samples, summed in the
 // reference's order). 16x8 tile per CTA; warp w → 8x4 patch (w&1, w>>1); lane → (lane&7, lane>>3),
 // so the lanes of a warp put near-identical queries to the scene and stay in the same phase of the
@@ -61,20 +95,19 @@ __global__ void __launch_bounds__(128, MINB) render_kernel(SceneView S, CameraD 
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   const uint32_t px = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
   const uint32_t oy = P.oy0 + blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
-  if (px >= cam.hsize || oy >= P.owned_rows) return;
+  bool alive = px < cam.hsize && oy < P.owned_rows;
   // owned row index → frame row: tile (rank + k*nranks), row within tile
   const uint32_t k = oy / P.tile_rows, r = oy - k * P.tile_rows;
   const uint32_t py = (P.rank + k * P.nranks) * P.tile_rows + r;
-  if (py < P.row_begin || py >= P.row_end) return;
+  alive = alive && py >= P.row_begin && py < P.row_end;
 
   Scratch<HAS_CSG> scratch;
   RayCounters rc = {0u, 0u, 0u, 0u};
   uint32_t err = 0;
-  V3 c = render_pixel<HAS_CSG, FAITHFUL>(S, cam, px, py, P.aa, P.average != 0, P.max_depth, scratch, rc, &err);
-  double* o = out + ((size_t)py * cam.hsize + px) * 3;  // Canvas::pixel_idx, canvas.rs:44-48
-  o[0] = c.x;
-  o[1] = c.y;
-  o[2] = c.z;
+  V3 c = v3(0.0, 0.0, 0.0);
+  if (alive) c = render_pixel<HAS_CSG, FAITHFUL>(S, cam, px, py, P.aa, P.average != 0, P.max_depth, scratch, rc, &err);
+  __syncwarp();
+  store_patch_row(out + ((size_t)py * cam.hsize + px) * 3, c, lane, alive);  // Canvas::pixel_idx, canvas.rs:44-48
   flush_counters(rc, err, counters);
 }
 
