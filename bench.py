@@ -129,6 +129,7 @@ def main():
     ap.add_argument("--tile-rows", type=int, default=8)
     ap.add_argument("--ref-rows", type=int, default=0, help="reference arm: render only this many rows (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-push-tiles", action="store_true", help="N >= 3: let every rank's kernels store into rank 0's canvas themselves")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -164,11 +165,11 @@ def main():
 
     gather = args.gather
     try:
-        sr = mg.ShardedRenderer(pkg, flat, cam, rank, world_size, local_rank, tile_rows=args.tile_rows, gather=gather, dist=dist)
+        sr = mg.ShardedRenderer(pkg, flat, cam, rank, world_size, local_rank, tile_rows=args.tile_rows, gather=gather, dist=dist, push_tiles=not args.no_push_tiles)
     except Exception as e:  # peer mapping unavailable → NCCL reduce
         if world_size > 1 and gather == "ipc":
             gather = "nccl"
-            sr = mg.ShardedRenderer(pkg, flat, cam, rank, world_size, local_rank, tile_rows=args.tile_rows, gather=gather, dist=dist)
+            sr = mg.ShardedRenderer(pkg, flat, cam, rank, world_size, local_rank, tile_rows=args.tile_rows, gather=gather, dist=dist, push_tiles=not args.no_push_tiles)
         else:
             raise
     stream = torch.cuda.current_stream()

@@ -218,6 +218,12 @@ RTC_API int rtc_canvas_export(rtc_canvas* canvas, unsigned char handle[64]);
 RTC_API int rtc_canvas_open(int device, const unsigned char handle[64], size_t n_doubles, rtc_canvas** out);
 RTC_API double* rtc_canvas_ptr(rtc_canvas* canvas);
 RTC_API int rtc_canvas_download(rtc_canvas* canvas, double* host, size_t offset_doubles, size_t n_doubles);
+/* Copy the tiles `rank` of `nranks` owns (tile t = rows [t*tile_rows, (t+1)*tile_rows), t % nranks == rank) from a
+ * local device canvas of the same shape into `canvas` (usually rank 0's, opened over IPC): one strided DMA over NVLink,
+ * queued on `stream`. The alternative to letting the kernels store into the peer canvas themselves: the wavefront
+ * renderer completes pixels in 24-byte pieces from many passes, which a peer mapping pays for piece by piece. */
+RTC_API int rtc_canvas_push_tiles(rtc_canvas* canvas, const double* local_dev, uint32_t hsize, uint32_t vsize,
+                                  uint32_t tile_rows, uint32_t rank, uint32_t nranks, void* stream);
 RTC_API void rtc_canvas_destroy(rtc_canvas* canvas);
 
 /* Debug / known-answer entry: Vector::normalize (vector.rs:25-28) of n host vectors (xyz triples) on

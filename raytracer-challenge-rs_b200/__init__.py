@@ -105,6 +105,7 @@ def cuda_lib():
         lib.rtc_canvas_ptr.argtypes = [vp]
         lib.rtc_canvas_ptr.restype = vp
         lib.rtc_canvas_download.argtypes = [vp, pd, sz, sz]
+        lib.rtc_canvas_push_tiles.argtypes = [vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, vp]
         lib.rtc_canvas_destroy.argtypes = [vp]
         lib.rtc_canvas_destroy.restype = None
         lib.rtc_measure_fp64.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double)]

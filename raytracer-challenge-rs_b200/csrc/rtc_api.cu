@@ -850,6 +850,26 @@ int rtc_canvas_download(rtc_canvas* c, double* host, size_t off, size_t n) {
   CUDA_TRY(cudaMemcpy(host, c->ptr + off, n * sizeof(double), cudaMemcpyDeviceToHost));
   return RTC_OK;
 }
+int rtc_canvas_push_tiles(rtc_canvas* c, const double* local_dev, uint32_t hsize, uint32_t vsize, uint32_t tile_rows,
+                          uint32_t rank, uint32_t nranks, void* stream_) {
+  if (!c || !local_dev || tile_rows == 0 || nranks == 0 || rank >= nranks) return fail(RTC_ERR_INVALID, "bad tile push");
+  if ((size_t)hsize * vsize * 3 > c->n) return fail(RTC_ERR_INVALID, "canvas too small for the frame");
+  CUDA_TRY(cudaSetDevice(c->device));
+  cudaStream_t stream = (cudaStream_t)stream_;
+  const size_t row_bytes = (size_t)hsize * 3 * sizeof(double), tile_bytes = row_bytes * tile_rows;
+  const uint32_t full_tiles = vsize / tile_rows;                       // tiles [0, full_tiles) are whole
+  const uint32_t mine = full_tiles > rank ? (full_tiles - rank + nranks - 1) / nranks : 0;
+  const size_t first = (size_t)rank * tile_bytes;
+  if (mine)
+    CUDA_TRY(cudaMemcpy2DAsync((char*)c->ptr + first, tile_bytes * nranks, (const char*)local_dev + first, tile_bytes * nranks,
+                               tile_bytes, mine, cudaMemcpyDeviceToDevice, stream));
+  if (vsize % tile_rows && full_tiles % nranks == rank) {              // the ragged last tile is this rank's
+    const size_t off = (size_t)full_tiles * tile_bytes;
+    CUDA_TRY(cudaMemcpyAsync((char*)c->ptr + off, (const char*)local_dev + off, row_bytes * (vsize % tile_rows),
+                             cudaMemcpyDeviceToDevice, stream));
+  }
+  return RTC_OK;
+}
 void rtc_canvas_destroy(rtc_canvas* c) {
   if (!c) return;
   cudaSetDevice(c->device);

@@ -29,13 +29,14 @@ def owned_row_mask(vsize, tile_rows, rank, nranks):
 class ShardedRenderer:
     """One rank's side of the sharded render. Needs torch with CUDA and an initialised process group."""
 
-    def __init__(self, pkg, flat, camera, rank, nranks, device, tile_rows=8, gather="ipc", dist=None):
+    def __init__(self, pkg, flat, camera, rank, nranks, device, tile_rows=8, gather="ipc", dist=None, push_tiles=True):
         import torch
         self.torch, self.pkg, self.dist = torch, pkg, dist
         self.rank, self.nranks, self.device, self.tile_rows = rank, nranks, device, tile_rows
         self.camera = pkg.camera_to_rtc(camera)
         self.scene = pkg.DeviceScene(flat, device=device)
         self.n = self.camera.hsize * self.camera.vsize * 3
+        self.push_tiles = push_tiles
         self.gather = gather if nranks > 1 else "local"
         self.canvas = None       # rtc_canvas handle (ipc) or torch tensor
         self.canvas_ptr = None
@@ -59,6 +60,12 @@ class ShardedRenderer:
                 pkg._check(lib.rtc_canvas_open(self.device, raw, self.n, C.byref(h)))
             self.canvas = h
             self.canvas_ptr = lib.rtc_canvas_ptr(h)
+            # >= 3 ranks: scenes that recurse are rendered as a wavefront, whose pixels complete in 24-byte pieces
+            # from many passes — ranks other than 0 then render into a local canvas and push their tiles to
+            # rank 0 with one strided DMA (rtc_canvas_push_tiles) instead of storing across NVLink piecewise
+            self.local = None
+            if self.rank != 0 and self.nranks >= 3 and self.push_tiles:
+                self.local = torch.zeros(self.n, dtype=torch.float64, device="cuda:%d" % self.device)
         else:
             self.canvas = torch.zeros(self.n, dtype=torch.float64, device="cuda:%d" % self.device)
             self.canvas_ptr = self.canvas.data_ptr()
@@ -67,15 +74,30 @@ class ShardedRenderer:
         """Queue this rank's tiles on `stream_ptr` (a cudaStream_t as int; torch's current stream)."""
         if self.gather == "nccl":
             self.canvas.zero_()  # rank 0 holds last step's gathered frame; the reduce needs disjoint supports
-        self.scene.render_device(self.camera, self.canvas_ptr, stream=stream_ptr, stats=False, aa=aa,
-                                 max_depth=max_depth, tile_rows=self.tile_rows, rank=self.rank, nranks=self.nranks)
+        local = getattr(self, "local", None)
+        self.scene.render_device(self.camera, local.data_ptr() if local is not None else self.canvas_ptr, stream=stream_ptr,
+                                 stats=False, aa=aa, max_depth=max_depth, tile_rows=self.tile_rows, rank=self.rank,
+                                 nranks=self.nranks)
+        if local is not None:
+            self.pkg._check(self.pkg.cuda_lib().rtc_canvas_push_tiles(self.canvas, local.data_ptr(), self.camera.hsize,
+                                                                      self.camera.vsize, self.tile_rows, self.rank,
+                                                                      self.nranks, stream_ptr))
 
     def gather_nccl(self):
         if self.gather == "nccl":
             self.dist.reduce(self.canvas, dst=0, op=self.dist.ReduceOp.SUM)
 
     def finish(self, stream_ptr):
-        return self.scene.finish(stream_ptr)
+        st = self.scene.finish(stream_ptr)
+        local = getattr(self, "local", None)
+        if local is not None and st.launches == 1:
+            # one launch: the recursive kernel ran — possibly as the overflow fallback inside finish(), after
+            # the tiles were pushed; push what is in the local canvas now
+            lib = self.pkg.cuda_lib()
+            self.pkg._check(lib.rtc_canvas_push_tiles(self.canvas, local.data_ptr(), self.camera.hsize, self.camera.vsize,
+                                                      self.tile_rows, self.rank, self.nranks, stream_ptr))
+            self.torch.cuda.synchronize()
+        return st
 
     def download(self, host_tensor):
         """rank 0: device canvas → pinned host tensor (float64[n])."""
