@@ -172,6 +172,35 @@ def test_row_range_and_cyclic_tiles(pkg, prod):
     ds.close()
 
 
+def test_canvas_push_tiles(pkg):
+    """rtc_canvas_push_tiles: exactly the tiles rank r of n owns (ragged last tile included) move from a local
+    canvas into the target canvas; everything else is left alone."""
+    import torch
+    lib = pkg.cuda_lib()
+    W, H, T = 40, 37, 8   # 4 whole tiles + a ragged one of 5 rows
+    n = W * H * 3
+    h = C.c_void_p()
+    pkg._check(lib.rtc_canvas_create(0, n, C.byref(h)))
+    host = torch.empty(n, dtype=torch.float64)
+    for nranks in (1, 2, 3):
+        for rank in range(nranks):
+            local = torch.arange(n, dtype=torch.float64, device="cuda") + 1.0
+            zero = torch.zeros(n, dtype=torch.float64, device="cuda")
+            # clear the target through the same call (rank 0 of 1 owns everything)
+            pkg._check(lib.rtc_canvas_push_tiles(h, zero.data_ptr(), W, H, T, 0, 1, None))
+            pkg._check(lib.rtc_canvas_push_tiles(h, local.data_ptr(), W, H, T, rank, nranks, None))
+            torch.cuda.synchronize()
+            pkg._check(lib.rtc_canvas_download(h, host.data_ptr(), 0, n))
+            got = host.numpy().reshape(H, W * 3)
+            want = np.zeros_like(got)
+            src = local.cpu().numpy().reshape(H, W * 3)
+            for y in range(H):
+                if (y // T) % nranks == rank:
+                    want[y] = src[y]
+            assert np.array_equal(got, want), (nranks, rank)
+    lib.rtc_canvas_destroy(h)
+
+
 def test_empty_world_and_no_lights(pkg, prod):
     w = prod.world()
     c = prod.camera(8, 4, 1.0)
