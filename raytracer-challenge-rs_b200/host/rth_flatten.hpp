@@ -67,8 +67,25 @@ class Flattener {
       std::memcpy(rl.intensity, l.intensity, sizeof rl.intensity);
       out_.lights.push_back(rl);
     }
+    // Size the tables before the walk: every node is some aggregate's child (or a top-level object), so visiting
+    // the aggregates alone (1/8 of a divided mesh) gives the exact node count; the triangle tables are bounded by
+    // it. Growing 180 MB of vectors by doubling re-copies them twice and faults every page twice.
+    size_t n_nodes = w.objects.size();
+    for (const ShapeP& s : w.objects) n_nodes += count_below(*s);
+    out_.nodes.reserve(n_nodes);
+    if (n_nodes > 4096) {
+      out_.tri_geom.reserve(9 * n_nodes);
+      out_.tri_normals.reserve(9 * n_nodes);
+    }
     for (const ShapeP& s : w.objects) emit(*s);
     return std::move(out_);
+  }
+  static size_t count_below(const Shape& s) {
+    if (s.kind != RTC_GROUP && s.kind != RTC_CSG) return 0;
+    size_t n = s.children.size();
+    for (const ShapeP& c : s.children)
+      if (c->kind == RTC_GROUP || c->kind == RTC_CSG) n += count_below(*c);
+    return n;
   }
 
  private:
