@@ -59,7 +59,7 @@ struct rtc_scene {
   size_t wave_bytes = 0;
   bool lean = false;           // every-ray spheres and planes only: the kernels without BVH / generic leaf code
   bool tri_sph_only = false;   // spheres/planes every ray + a BVH of triangles and spheres: no generic leaf code
-  bool has_secondary = false;  // some material reflects or refracts: color_at recurses (world.rs:107-134)
+  bool has_branching = false;  // some material reflects AND refracts: shade_hit spawns two children, the tree grows as 2^depth
   bool last_wave = false;
   CameraD last_cam{};
   RenderParams last_P{};
@@ -336,10 +336,12 @@ int launch_wave(rtc_scene* s, const CameraD& cam, const RenderParams& P, double*
 
 // RTC_WAVEFRONT=0/1 in the environment overrides the choice (experiments); otherwise RTC_OPT_WAVEFRONT /
 // RTC_OPT_RECURSIVE in rtc_opts.flags, otherwise the measured default.
-// Default (measured, profiles/r01g_*): on a whole 1080p frame the recursive kernel is faster (no queue
-// traffic, 2.9 vs 3.3 ms on the glass scene); once the frame is split over >= RTK_WAVE_MIN_RANKS GPUs its
-// serial per-pixel recursion is the critical path (1.16 ms for an eighth of that frame, 0.5 ms as a
-// wavefront). Scenes without reflective or transparent materials never recurse and stay recursive.
+// Default (measured, profiles/r01h_shard_probe.log, r01k_ncu_teapot_summary.md): on a whole frame the recursive kernel
+// is faster (no queue traffic: 2.06 vs 2.62 ms on the glass scene); once the frame is split over >= RTK_WAVE_MIN_RANKS
+// GPUs the serial recursion of a pixel whose hits spawn TWO children (a material that reflects and refracts: up to
+// 63 calls at depth 5) is the critical path — 0.81 ms for an eighth of that frame, 0.48 ms as a wavefront. Mirror-only or
+// glass-only scenes recurse in chains of at most max_depth + 1 calls; there a single heavy BVH query bounds the
+// frame and the wavefront only adds traffic (teapot scene, an eighth: 1.64 vs 2.29 ms), so they stay recursive.
 bool use_wavefront(const rtc_scene* s, const RenderParams& P, bool faithful, uint32_t flags) {
   if (faithful || P.aa != 1 || P.average || P.max_depth < 1) return false;
   static const char* env = std::getenv("RTC_WAVEFRONT");
@@ -347,7 +349,7 @@ bool use_wavefront(const rtc_scene* s, const RenderParams& P, bool faithful, uin
   if (env && env[0] == '1') return true;
   if (flags & RTC_OPT_RECURSIVE) return false;
   if (flags & RTC_OPT_WAVEFRONT) return true;
-  return s->has_secondary && P.nranks >= RTK_WAVE_MIN_RANKS;
+  return s->has_branching && P.nranks >= RTK_WAVE_MIN_RANKS;
 }
 
 int launch_frame(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool faithful, double* out, cudaStream_t stream) {
@@ -469,9 +471,10 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   s->device = device;
   s->has_csg = has_csg;
   for (uint32_t m = 0; m < d->n_materials; m++)
-    if (d->materials[m].reflective != 0.0 || d->materials[m].transparency != 0.0) s->has_secondary = true;
+    if (d->materials[m].reflective != 0.0 && d->materials[m].transparency != 0.0) s->has_branching = true;
   // 126 MB of L2 on B200: past ~64 MB of nodes + leaf records, traversal is DRAM-latency bound
   s->big_accel = sizeof(BvhNode) * accel.bvh.size() + sizeof(LeafRec) * accel.leaf_recs.size() > ((size_t)64 << 20);
+  if (const char* env = std::getenv("RTC_BIG_ACCEL")) s->big_accel = env[0] == '1';  // experiments: force the 32-warp kernels on/off
   s->slab_bytes = total;
   auto bail = [&](cudaError_t e, const char* what) {
     std::string m = std::string(what) + ": " + cudaGetErrorString(e);

@@ -182,3 +182,26 @@ EMUL_API int emul_is_shadowed(const rtc_scene_desc* d, const double* p, uint32_t
 }
 
 }  // extern "C"
+
+#if defined(RTK_STATS)
+// Diagnostic build only (-DRTK_STATS): per-pixel search cost (BVH nodes, prim tests, reference-box validations) of
+// the accelerated renderer, single-threaded. cost[pixel*4 + {0,1,2,3}] = walks, bvh_nodes, prim_tests, chain_boxes.
+extern "C" EMUL_API int emul_cost_map(const rtc_scene_desc* d, const rtc_camera* c, const rtc_opts* o, uint64_t* cost) {
+  Built b;
+  build_view(d, b);
+  CameraD cam = make_cam(c);
+  if (b.view.has_csg) return -1;
+  Scratch<false>* scratch = new Scratch<false>();
+  for (uint32_t y = 0; y < c->vsize; y++)
+    for (uint32_t x = 0; x < c->hsize; x++) {
+      accel_stats() = AccelStats();
+      RayCounters rc = {0, 0, 0, 0};
+      uint32_t err = 0;
+      render_pixel<false, false>(b.view, cam, x, y, 1, false, (int)o->max_depth, *scratch, rc, &err);
+      uint64_t* q = cost + ((size_t)y * c->hsize + x) * 4;
+      q[0] = accel_stats().walks; q[1] = accel_stats().bvh_nodes; q[2] = accel_stats().prim_tests; q[3] = accel_stats().chain_boxes;
+    }
+  delete scratch;
+  return 0;
+}
+#endif
