@@ -22,6 +22,7 @@ struct RenderParams {
   int32_t max_depth;
   uint32_t faithful;             // RTC_OPT_FAITHFUL_TRAVERSAL: the reference's own search order
   uint32_t flags;                // rtc_opts.flags
+  const uint32_t* order;         // CTA dispatch order: order[linear block id] = tile_y << 16 | tile_x (NULL: row-major)
 };
 
 // counters[0..3] rays primary/shadow/reflect/refract, [4] overflow pixels, [5] NaN pixels
@@ -93,8 +94,17 @@ template <bool HAS_CSG, int FAITHFUL, int MINB = RTK_MIN_BLOCKS>
 __global__ void __launch_bounds__(128, MINB) render_kernel(SceneView S, CameraD cam, RenderParams P, double* __restrict__ out,
                                                                      unsigned long long* __restrict__ counters) {
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-  const uint32_t px = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
-  const uint32_t oy = P.oy0 + blockIdx.y * 8u + (warp >> 1) * 4u + (lane >> 3);
+  // CTAs are dispatched in linear block order; `order` maps that order to tiles, centre of the image first: the
+  // heaviest warps of a frame (glass, mesh silhouettes: 1 ms chains) usually sit near the centre, and a chain that
+  // starts at t = 0 hides behind the rest of the frame instead of sticking out of its end
+  uint32_t bx = blockIdx.x, by = blockIdx.y;
+  if (P.order) {
+    const uint32_t t = __ldg(P.order + blockIdx.y * gridDim.x + blockIdx.x);
+    bx = t & 0xffffu;
+    by = t >> 16;
+  }
+  const uint32_t px = bx * 16u + (warp & 1u) * 8u + (lane & 7u);
+  const uint32_t oy = P.oy0 + by * 8u + (warp >> 1) * 4u + (lane >> 3);
   bool alive = px < cam.hsize && oy < P.owned_rows;
   // owned row index → frame row: tile (rank + k*nranks), row within tile
   const uint32_t k = oy / P.tile_rows, r = oy - k * P.tile_rows;

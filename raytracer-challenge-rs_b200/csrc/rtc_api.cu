@@ -2,6 +2,7 @@
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo --fmad=false -Xcompiler -fPIC,-ffp-contract=off
 //        -shared -o librtc_cuda.so rtc_api.cu
 // No CPU fallback: every compute entry point needs a CUDA device.
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -186,6 +187,35 @@ int make_params(const rtc_camera* c, const rtc_opts* o, RenderParams& P, bool& f
   return RTC_OK;
 }
 
+// Centre-out dispatch order of a gx x gy grid of tiles, cached per (device, gx, gy) for the life of the process
+// (64 KB at 1080p; building it costs a sort, which the per-step scene of the end-to-end path must not pay).
+struct OrderCache {
+  std::mutex mu;
+  struct Entry { int dev; uint32_t gx, gy; uint32_t* ptr; };
+  std::vector<Entry> entries;
+  const uint32_t* get(int dev, uint32_t gx, uint32_t gy) {
+    if (gx == 0 || gy == 0 || gx > 0xffffu || gy > 0xffffu) return nullptr;
+    std::lock_guard<std::mutex> g(mu);
+    for (const Entry& e : entries)
+      if (e.dev == dev && e.gx == gx && e.gy == gy) return e.ptr;
+    std::vector<std::pair<double, uint32_t>> key((size_t)gx * gy);
+    for (uint32_t y = 0; y < gy; y++)
+      for (uint32_t x = 0; x < gx; x++) {
+        const double dx = (x + 0.5) / gx - 0.5, dy = (y + 0.5) / gy - 0.5;
+        key[(size_t)y * gx + x] = {dx * dx + dy * dy, (y << 16) | x};
+      }
+    std::stable_sort(key.begin(), key.end(), [](const std::pair<double, uint32_t>& a, const std::pair<double, uint32_t>& b) { return a.first < b.first; });
+    std::vector<uint32_t> h(key.size());
+    for (size_t i = 0; i < key.size(); i++) h[i] = key[i].second;
+    uint32_t* d = nullptr;
+    if (cudaMalloc((void**)&d, h.size() * sizeof(uint32_t)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (cudaMemcpy(d, h.data(), h.size() * sizeof(uint32_t), cudaMemcpyHostToDevice) != cudaSuccess) { cudaGetLastError(); cudaFree(d); return nullptr; }
+    entries.push_back({dev, gx, gy, d});
+    return d;
+  }
+};
+OrderCache g_order_cache;
+
 // One launch over owned rows [oy0, oy0 + rows) of the launch domain (rows == 0: the whole domain).
 int launch_rows(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool faithful, double* out, cudaStream_t stream,
                 uint32_t oy0, uint32_t rows) {
@@ -195,6 +225,10 @@ int launch_rows(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool fa
   if (rows == 0) rows = P.owned_rows > oy0 ? P.owned_rows - oy0 : 0;
   if (oy0 + rows < Pk.owned_rows) Pk.owned_rows = oy0 + rows;
   dim3 block(128), grid((cam.hsize + 15) / 16, (rows + 7) / 8);
+  {
+    static const char* env = std::getenv("RTC_TILE_ORDER");  // 0: row-major (experiments)
+    Pk.order = (env && env[0] == '0') ? nullptr : g_order_cache.get(s->device, grid.x, grid.y);
+  }
   if (grid.x > 0 && grid.y > 0) {
     if (s->has_csg) {
       if (faithful) render_kernel<true, true><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
@@ -584,7 +618,7 @@ int rtc_render_device(rtc_scene* s, const rtc_camera* camera, const rtc_opts* op
   if (!s || !rgb_dev) return fail(RTC_ERR_INVALID, "NULL scene or canvas");
   auto t0 = std::chrono::steady_clock::now();
   CameraD cam;
-  RenderParams P;
+  RenderParams P{};
   bool faithful = false;
   int rc = make_camera(camera, cam);
   if (rc) return rc;
@@ -641,7 +675,7 @@ int rtc_render(rtc_scene* s, const rtc_camera* camera, const rtc_opts* opts, dou
   if (!s || !rgb_host) return fail(RTC_ERR_INVALID, "NULL scene or canvas");
   auto t0 = std::chrono::steady_clock::now();
   CameraD cam;
-  RenderParams P;
+  RenderParams P{};
   bool faithful = false;
   int rc = make_camera(camera, cam);
   if (rc) return rc;
@@ -719,7 +753,7 @@ int rtc_render_rgb8(rtc_scene* s, const rtc_camera* camera, const rtc_opts* opts
   if (!s || !rgb8_host) return fail(RTC_ERR_INVALID, "NULL scene or image");
   auto t0 = std::chrono::steady_clock::now();
   CameraD cam;
-  RenderParams P;
+  RenderParams P{};
   bool faithful = false;
   int rc = make_camera(camera, cam);
   if (rc) return rc;
