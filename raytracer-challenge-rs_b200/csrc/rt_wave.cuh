@@ -55,7 +55,8 @@ struct WaveLevel {
 };
 struct WaveArgs {
   WaveLevel lv[WAVE_MAX_LEVELS + 1];
-  uint32_t* n_items;      // device counters, one per level
+  unsigned long long* n_items;  // per level: low word = reflection items (stored from the front of the level's
+                                // queue), high word = refraction items (stored from its END downwards); one atomic
   uint32_t* n_recs;
   uint32_t* work;         // per pass: items handed out so far
   int32_t level;          // the level whose queue this pass drains
@@ -90,7 +91,16 @@ __global__ void __launch_bounds__(128, MINB) wave_forward_kernel(SceneView S, Ca
   const int l = PRIMARY ? 0 : A.level;
   // patches: 8 px wide, 4 rows tall over the owned-row domain
   const uint32_t pw = (cam.hsize + 7u) >> 3, ph = (P.owned_rows + 3u) >> 2;
-  const uint32_t n = PRIMARY ? pw * ph * 32u : min(A.n_items[l], A.lv[l].cap_items);
+  // A level's queue holds the reflection rays from its front and the refraction rays from its end: the warps of
+  // the next pass are then all-reflection (wall hits: closest + shadow) or all-refraction (inside glass:
+  // closest + containers) and their lanes finish together far more often.
+  uint32_t n_front = 0, n_rear = 0;
+  if (!PRIMARY) {
+    const unsigned long long q = A.n_items[l];
+    n_front = min((uint32_t)q, A.lv[l].cap_items);
+    n_rear = min((uint32_t)(q >> 32), A.lv[l].cap_items - n_front);
+  }
+  const uint32_t n = PRIMARY ? pw * ph * 32u : n_front + n_rear;
   uint32_t parent = 0, slot = 0;
   // item idx of this pass → this lane's ray / parent / slot; false: nothing to trace (pixel outside the frame)
   auto load_item = [&](uint32_t idx, RayD& ray) -> bool {
@@ -104,7 +114,8 @@ __global__ void __launch_bounds__(128, MINB) wave_forward_kernel(SceneView S, Ca
       ray = ray_for_pixel(cam, px, py, 0.5, 0.5);
       parent = py * cam.hsize + px;  // Canvas::pixel_idx, canvas.rs:44-48
     } else {
-      const double2* q = reinterpret_cast<const double2*>(A.lv[l].items + idx);
+      const uint32_t at = idx < n_front ? idx : A.lv[l].cap_items - 1u - (idx - n_front);
+      const double2* q = reinterpret_cast<const double2*>(A.lv[l].items + at);
       const double2 a = __ldcs(q), b = __ldcs(q + 1), c = __ldcs(q + 2);
       const int4 h = __ldcs(reinterpret_cast<const int4*>(q + 3));
       ray.o = v3(a.x, a.y, b.x); ray.d = v3(b.y, c.x, c.y);
@@ -120,17 +131,22 @@ __global__ void __launch_bounds__(128, MINB) wave_forward_kernel(SceneView S, Ca
     const unsigned m_refl = __ballot_sync(m, has_reflect), m_refr = __ballot_sync(m, has_refr);
     const int leader = __ffs(m) - 1;
     uint32_t rec0 = 0, item0 = 0;
+    const uint32_t g_refl = __popc(m_refl), g_refr = __popc(m_refr);
+    unsigned long long q0 = 0;
     if ((int)lane == leader) {
       rec0 = atomicAdd(A.n_recs + l, (uint32_t)__popc(m));
-      item0 = atomicAdd(A.n_items + l + 1, (uint32_t)(__popc(m_refl) + __popc(m_refr)));
+      q0 = atomicAdd(A.n_items + l + 1, ((unsigned long long)g_refr << 32) | g_refl);  // both ends in one atomic
     }
     rec0 = __shfl_sync(m, rec0, leader);
-    item0 = __shfl_sync(m, item0, leader);
+    q0 = __shfl_sync(m, q0, leader);
+    const uint32_t front0 = (uint32_t)q0, back0 = (uint32_t)(q0 >> 32);
     const uint32_t lt = (1u << lane) - 1u;
     const uint32_t ri = rec0 + __popc(m & lt);
-    const uint32_t i_refl = item0 + __popc(m_refl & lt), i_refr = item0 + __popc(m_refl) + __popc(m_refr & lt);
     const uint32_t cap = A.lv[l + 1].cap_items;
-    if (ri >= A.lv[l].cap_recs || (has_reflect && i_refl >= cap) || (has_refr && i_refr >= cap)) { dropped++; return; }
+    // the two ends have not met iff everything reserved so far, this group included, fits the queue
+    if (ri >= A.lv[l].cap_recs || (unsigned long long)front0 + g_refl + back0 + g_refr > cap) { dropped++; return; }
+    const uint32_t i_refl = front0 + __popc(m_refl & lt), i_refr = cap - 1u - (back0 + __popc(m_refr & lt));
+    (void)item0;
     double2* R = reinterpret_cast<double2*>(A.lv[l].recs + ri);
     R[0] = make_double2(f.surface.x, f.surface.y);
     R[1] = make_double2(f.surface.z, f.reflective);
