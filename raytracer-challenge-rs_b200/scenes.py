@@ -9,7 +9,7 @@ import math
 import numpy as np
 
 from . import transform as T
-from .api import (DIFFERENCE, Material, checkers_pattern, ring_pattern, stripe_pattern)
+from .api import (DIFFERENCE, Material, checkers_pattern, gradient_pattern, ring_pattern, stripe_pattern, test_pattern)
 
 PI = math.pi
 
@@ -403,6 +403,47 @@ def solids_field(api, width=640, height=360):
     return w, cam
 
 
+def pattern_gallery(api, width=640, height=360):
+    """Parity case for the pattern kinds no reference scene file uses: gradient (pattern/gradient.rs:14-18) on a
+    plane, a sphere (with a pattern transform) and a cube, the test pattern (test_pattern.rs:7-9) on a cylinder, a
+    ring-patterned cone and a stripe-patterned mirror sphere; two lights."""
+    w = api.world()
+    w.add_light((-6, 8, -8), (0.9, 0.9, 0.9))
+    w.add_light((7, 5, -6), (0.3, 0.25, 0.35))
+    w.add_object(api.plane().set_material(Material(
+        pattern=gradient_pattern((0.9, 0.2, 0.1), (0.1, 0.3, 0.9)).set_transform(T.chain(T.scaling(3.0, 1.0, 1.0), T.rotation_y(0.4))),
+        reflective=0.15, specular=0.2)))
+    w.add_object(api.sphere().set_transform(T.translation(-2.2, 1.0, 0.5))
+                 .set_material(Material(pattern=gradient_pattern((1.0, 1.0, 0.0), (0.0, 0.6, 0.2))
+                                        .set_transform(T.chain(T.scaling(0.5, 0.5, 0.5), T.rotation_z(0.7), T.translation(0.25, 0, 0))),
+                                        diffuse=0.8, specular=0.4, shininess=50.0)))
+    w.add_object(api.cube().set_transform(T.chain(T.scaling(0.7, 0.7, 0.7), T.rotation_y(0.6), T.translation(0.0, 0.7, 1.5)))
+                 .set_material(Material(pattern=gradient_pattern((0.2, 0.2, 0.2), (1.0, 1.0, 1.0)), transparency=0.3,
+                                        refractive_index=1.2)))
+    w.add_object(api.cylinder(0.0, 1.5, True).set_transform(T.chain(T.scaling(0.6, 1.0, 0.6), T.translation(2.2, 0.0, 0.2)))
+                 .set_material(Material(pattern=test_pattern().set_transform(T.scaling(2.0, 1.5, 2.0)), ambient=0.3, diffuse=0.6)))
+    w.add_object(api.cone(-1.0, 0.0, True).set_transform(T.chain(T.scaling(0.8, 1.4, 0.8), T.translation(0.8, 1.4, -1.4)))
+                 .set_material(Material(pattern=ring_pattern((0.9, 0.9, 0.9), (0.1, 0.1, 0.5)).set_transform(T.scaling(0.2, 0.2, 0.2)))))
+    w.add_object(api.sphere().set_transform(T.chain(T.scaling(0.6, 0.6, 0.6), T.translation(-0.8, 0.6, -1.6)))
+                 .set_material(Material(pattern=stripe_pattern((0.8, 0.1, 0.1), (0.95, 0.95, 0.95)).set_transform(
+                     T.chain(T.scaling(0.2, 0.2, 0.2), T.rotation_z(0.5))), reflective=0.5)))
+    cam = api.camera(width, height, 1.0)
+    cam.set_transform(T.view_transform((0.5, 3.0, -7.0), (0, 0.8, 0), (0, 1, 0)))
+    return w, cam
+
+
+def cone_field(api):
+    """Cones for the `abs(a) < EPSILON` branch of Cone::local_intersect (cone.rs:102-110, with its `-c / 2.0 * b`):
+    untransformed and translated only, so that a world direction proportional to (0, 1, 1) has a == 0 in object space."""
+    w = api.world()
+    w.add_light((-10, 10, -10), (1, 1, 1))
+    w.add_object(api.cone().set_material(Material(color=(0.9, 0.4, 0.2))))
+    w.add_object(api.cone(-1.0, 2.0, True).set_transform(T.translation(4.0, 0.0, 0.0)).set_material(Material(color=(0.2, 0.4, 0.9), reflective=0.3)))
+    w.add_object(api.cone(-0.5, 0.5, False).set_transform(T.translation(-4.0, 1.0, 1.0)).set_material(Material(color=(0.2, 0.9, 0.3))))
+    w.add_object(api.plane().set_transform(T.translation(0, -3.0, 0)).set_material(Material(pattern=checkers_pattern((0.2, 0.2, 0.2), (0.8, 0.8, 0.8)))))
+    return w
+
+
 CONFIGS = {
     "default_world": default_world,
     "chapter7": chapter7,                # config 1
@@ -412,6 +453,7 @@ CONFIGS = {
     "glass_sphere2": glass_sphere2,
     "hexagon": hexagon,
     "solids_field": solids_field,
+    "pattern_gallery": pattern_gallery,
     "teapot_standin": teapot_standin,    # config 4
     "mesh_and_spheres": mesh_and_spheres,  # config 5
 }

@@ -11,6 +11,11 @@ SMALL_CASES = [
     ("solids_field", dict(width=160, height=90), 1),
     ("reflect_refract", dict(width=64, height=36), 4),
     ("glass_sphere2", dict(width=32, height=32, aa=16), 16),
+    # round 2: the pattern kinds and the aa tables (camera.rs:95 x2, :97-106 x8) that nothing exercised
+    ("pattern_gallery", dict(width=160, height=90), 1),
+    ("chapter7", dict(width=64, height=32), 2),
+    ("primitives_csg", dict(width=64, height=36), 8),
+    ("pattern_gallery", dict(width=48, height=27), 2),
 ]
 MESH_CASES = [
     ("teapot_standin", dict(width=96, height=54, segments=16, rings=12, nu=20, nv=16), 1),

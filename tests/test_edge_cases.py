@@ -1,0 +1,165 @@
+"""Code paths no scene file reaches, CPU tier (kernel source on the host) and GPU tier (C-ABI) against the oracle:
+the cone's |a| < EPSILON branch (cone.rs:102-110 — the reference has no test for it, so it is oracle-defined), the
+32-warp `big_accel` kernel instantiations (RTC_BIG_ACCEL=1), and the two device error reports actually firing:
+RTC_ERR_NAN (a NaN t reaches the sort: intersection.rs:113 panics) and RTC_ERR_OVERFLOW (bounded lists, cap 64)."""
+import importlib
+
+import numpy as np
+import pytest
+
+from conftest import compare_images
+from scene_cases import MESH_CASES, SMALL_CASES, case_id
+
+scenes = importlib.import_module("raytracer-challenge-rs_b200.scenes")
+
+R2 = 2.0 ** 0.5 / 2.0
+
+
+def cone_rays():
+    """Directions with dx^2 - dy^2 + dz^2 == 0 exactly ((0,±1,±1)/sqrt2 and (±1,±1,0)/sqrt2 have equal squares), over
+    origins that give b != 0 (one root: t = -c/2*b) and b == 0 (caps only); plus near-degenerate directions."""
+    rng = np.random.default_rng(20261105)
+    dirs = [(0, R2, R2), (0, -R2, R2), (0, R2, -R2), (0, -R2, -R2), (R2, R2, 0), (-R2, R2, 0), (R2, -R2, 0), (-R2, -R2, 0),
+            (0, 1, 1), (0, -1, 1), (1, -1, 0), (0.5, -R2, 0.5)]
+    o, d = [], []
+    for dv in dirs:
+        for _ in range(40):
+            o.append(rng.uniform(-2.5, 2.5, 3))
+            d.append(dv)
+        for c in ((0, 0, 0), (4, 0, 0), (-4, 1, 1)):       # on an axis apex: b == 0 and c == 0
+            o.append(c)
+            d.append(dv)
+        for c in ((0, 0.5, 0.5), (4, -0.25, 0.25)):         # oy*dy == oz*dz → b == 0
+            o.append(c)
+            d.append(dv)
+    o, d = np.array(o, dtype=np.float64), np.array(d, dtype=np.float64)
+    # near-degenerate: a = O(1e-6) straddling EPSILON = 1e-5
+    eps = rng.uniform(-3e-5, 3e-5, size=(200, 1))
+    o2 = rng.uniform(-2.5, 2.5, size=(200, 3))
+    d2 = np.tile(np.array([[0.0, R2, R2]]), (200, 1)) + np.concatenate([np.zeros((200, 1)), eps, np.zeros((200, 1))], axis=1)
+    return np.concatenate([o, o2]), np.concatenate([d, d2])
+
+
+def test_cone_parallel_branch_kernel_source(pkg, prod, orc, emul):
+    o, d = cone_rays()
+    rgb0, t0 = orc.trace_rays(scenes.cone_field(orc.api), o, d)
+    rgb1, t1 = emul.trace_rays(pkg.FlatScene(scenes.cone_field(prod)), o, d)
+    assert np.sum(t0 >= 0) > 100                      # the branch really produces hits
+    assert np.array_equal(t1, t0) and np.array_equal(rgb1, rgb0)
+
+
+@pytest.mark.gpu
+def test_cone_parallel_branch_gpu(pkg, prod, orc):
+    o, d = cone_rays()
+    rgb0, t0 = orc.trace_rays(scenes.cone_field(orc.api), o, d)
+    ds = pkg.DeviceScene(pkg.FlatScene(scenes.cone_field(prod)))
+    rgb1, t1 = ds.trace_rays(o, d)
+    assert np.array_equal(t1, t0)
+    assert np.max(np.abs(rgb1 - rgb0)) <= 1e-12
+    ds.close()
+    # and through the accelerated search (render path): a camera looking along (0,-1,1)/sqrt2 at the cones
+    for api_, kind in ((orc.api, "o"), (prod, "p")):
+        w = scenes.cone_field(api_)
+        c = api_.camera(64, 48, 0.9)
+        c.set_transform(pkg.transform.view_transform((0, 4, -4), (0, 0, 0), (0, 1, 0)))
+        if kind == "o":
+            want, iw = orc.render(c, w, threads=0)
+        else:
+            got, st, _ = pkg.render(c, w, device=0)
+    assert st.rays == iw["rays"]
+    frac, max8, lin = compare_images(got, want, orc.quantize)
+    assert frac == 1.0 and lin <= 1e-12, (frac, max8, lin)
+
+
+BIG_CASES = [MESH_CASES[0], MESH_CASES[1], ("primitives_csg", dict(width=96, height=54), 1), ("solids_field", dict(width=96, height=54), 1)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", BIG_CASES, ids=case_id)
+def test_big_accel_instantiations_match_oracle(case, pkg, prod, orc, monkeypatch):
+    """render_kernel<..,8> / wave_forward_kernel<..,8,..> (64 registers, 32 warps per SM) are picked only when the BVH
+    exceeds 64 MB — the 1 M-triangle scene; RTC_BIG_ACCEL=1 pushes the small cases through them, recursive and wavefront."""
+    name, kw, aa = case
+    wo, co = scenes.CONFIGS[name](orc.api, **kw)
+    want, iw = orc.render(co, wo, aa=aa, threads=0)
+    monkeypatch.setenv("RTC_BIG_ACCEL", "1")
+    wp, cp = scenes.CONFIGS[name](prod, **kw)
+    ds = pkg.DeviceScene(pkg.FlatScene(wp))
+    for wavefront in (False, True):
+        got, st = ds.render(cp, aa=aa, wavefront=wavefront)
+        assert st.launches == (11 if wavefront else 1)
+        assert (st.rays_primary, st.rays_shadow, st.rays_reflect, st.rays_refract) == \
+            (iw["rays_primary"], iw["rays_shadow"], iw["rays_reflect"], iw["rays_refract"]), wavefront
+        frac, max8, lin = compare_images(got, want, orc.quantize)
+        assert frac >= 0.999 and max8 <= 1 and lin <= 1e-12, (wavefront, frac, max8, lin)
+    ds.close()
+
+
+def nested_glass(api, pkg, n):
+    """n concentric glass spheres seen from inside the innermost: the containers walk of prepare_computations
+    (intersection.rs:63-90) meets n negative-t entries before the hit."""
+    w = api.world()
+    w.add_light((0, 0, 0), (1, 1, 1))
+    for k in range(n):
+        r = 1.0 + 0.05 * k
+        w.add_object(api.sphere().set_transform(pkg.transform.scaling(r, r, r))
+                     .set_material(pkg.Material(color=(0.2, 0.2, 0.2), transparency=0.9, reflective=0.5, refractive_index=1.0 + 0.01 * (k + 1))))
+    return w
+
+
+@pytest.mark.gpu
+def test_overflow_and_nan_are_reported(pkg, prod, orc):
+    T = pkg.transform
+    # 60 nested shells fit the bounded negative-t list (cap 64) and match the oracle ...
+    o = np.array([[0.0, 0.0, 0.0]])
+    d = np.array([[0.0, 0.0, 1.0]])
+    ds = pkg.DeviceScene(pkg.FlatScene(nested_glass(prod, pkg, 60)))
+    rgb1, t1 = ds.trace_rays(o, d, remaining=1)
+    rgb0, t0 = orc.trace_rays(nested_glass(orc.api, pkg, 60), o, d, remaining=1)
+    assert np.array_equal(t1, t0) and np.max(np.abs(rgb1 - rgb0)) <= 1e-12
+    ds.close()
+    # ... 70 do not: reported, never silently truncated — by the ray-batch entry and by a whole frame
+    w = nested_glass(prod, pkg, 70)
+    ds = pkg.DeviceScene(pkg.FlatScene(w))
+    with pytest.raises(pkg.RtcError) as e:
+        ds.trace_rays(o, d, remaining=1)
+    assert e.value.code == -3                              # RTC_ERR_OVERFLOW
+    c = prod.camera(16, 16, 0.5)
+    c.set_transform(T.view_transform((0, 0, 0), (0, 0, 1), (0, 1, 0)))
+    for wavefront in (False, True):
+        with pytest.raises(pkg.RtcError) as e:
+            ds.render(c, wavefront=wavefront)
+        assert e.value.code == -3
+    ds.close()
+    # a zero direction makes the sphere's t = (-0 ± 0) / 0 = NaN: the reference panics in the sort
+    # (intersection.rs:113), the oracle throws, the device reports RTC_ERR_NAN
+    wd, _ = scenes.default_world(prod)
+    ds = pkg.DeviceScene(pkg.FlatScene(wd))
+    z = np.array([[0.0, 0.0, 0.0]])
+    with pytest.raises(pkg.RtcError) as e:
+        ds.trace_rays(np.array([[0.0, 0.0, -5.0]]), z)
+    assert e.value.code == -4                              # RTC_ERR_NAN
+    with pytest.raises(RuntimeError):
+        orc.trace_rays(scenes.default_world(orc.api)[0], np.array([[0.0, 0.0, -5.0]]), z)
+    # a degenerate camera (pixel == origin → normalize(0) = NaN direction) does the same to a whole frame
+    c = prod.camera(8, 8, 0.5)
+    cam = pkg.camera_to_rtc(c)
+    for i in range(16):
+        cam.inverse[i] = 0.0
+    import ctypes as C
+    out = np.zeros((8, 8, 3))
+    st = pkg.RtcStats()
+    opts = pkg.make_opts()
+    rc = pkg.cuda_lib().rtc_render(ds.h, C.byref(cam), C.byref(opts), out.ctypes.data, C.byref(st))
+    assert rc == -4 and st.nan_count > 0
+    ds.close()
+
+
+def test_overflow_is_reported_by_kernel_source(pkg, prod, emul):
+    import ctypes as C
+    flat = pkg.FlatScene(nested_glass(prod, pkg, 70))
+    o = np.array([[0.0, 0.0, 0.0]])
+    d = np.array([[0.0, 0.0, 1.0]])
+    rgb, t = np.zeros_like(o), np.zeros(1)
+    err = emul.lib.emul_trace_rays(C.byref(flat.desc), 1, o.ctypes.data, d.ctypes.data, 1, rgb.ctypes.data, t.ctypes.data)
+    assert err & 1                                         # ERR_OVERFLOW
