@@ -69,6 +69,20 @@ struct SphCull {
   double _pad;
 };
 
+// Cube::check_axis (cube.rs:30-48) treats an object-space direction component below EPSILON as parallel: the slab
+// becomes "all of the line or none of it" by the ORIGIN's coordinate alone, so the reference reports hits whose point
+// lies outside the cube by up to EPSILON * t. No box bounds those, so a ray that is near-parallel to a face family of
+// some cube in the BVH must not be culled away from cubes. The face families (unit normals u, and the largest
+// theta = EPSILON / |row| of the cubes sharing u: |row . d| < EPSILON  <=>  |u . d| < theta) travel in SceneView; a ray
+// with (u . d)^2 < th2 + 1e-24 d.d for some family descends into every BVH child whose subtree holds a cube
+// (BVH_CUBE_BIT of c0 / c1) regardless of the box test. More than CUBE_DIR_MAX families: cubes stay every-ray prims.
+constexpr int CUBE_DIR_MAX = 6;
+constexpr int32_t BVH_CUBE_BIT = 1 << 30;
+struct CubeDir {
+  double ux, uy, uz;
+  double th2;  // 2 * theta^2 * (1 + 1e-6): (a + b)^2 <= 2 a^2 + 2 b^2 covers the clustering tolerance of u
+};
+
 struct AccelBuild {
   std::vector<LeafRec> leaf_recs;  // one per BVH prim: prims[n_always + k] ↔ leaf_recs[k]
   std::vector<PrimRec> recs;       // one per always-prim, same order as prims[0, n_always)
@@ -79,6 +93,8 @@ struct AccelBuild {
   std::vector<BvhNode> bvh;        // node 0 = root (empty vector: no BVH)
   int32_t max_depth = 0;
   SphCull sph_cull[SPH_CULL_MAX];
+  CubeDir cube_dirs[CUBE_DIR_MAX] = {};
+  int32_t n_cube_dirs = 0;
 };
 
 namespace accel_detail {
@@ -141,7 +157,8 @@ struct FwdCache {
   }
 };
 
-inline bool leaf_world_box(const rtc_scene_desc* d, const rtc_node& nd, Box& out, FwdCache& cache) {
+inline bool leaf_world_box(const rtc_scene_desc* d, const rtc_node& nd, Box& out, FwdCache& cache, bool cubes_ok = true) {
+  if (nd.kind == RTC_CUBE && !cubes_ok) return false;
   const double* fwd = cache.get(d, nd.xform);
   if (!fwd) return false;
   out.reset();
@@ -155,7 +172,7 @@ inline bool leaf_world_box(const rtc_scene_desc* d, const rtc_node& nd, Box& out
     xf(fwd, p3, w); out.add(w);
   } else if (nd.kind == RTC_SPHERE || nd.kind == RTC_CUBE || nd.kind == RTC_CYLINDER) {
     // object-space extent: the unit box; a cylinder is radius 1 between its limits (cylinder.rs:27-40)
-    // — an unbounded one stays an every-ray prim. Cones are never admitted: for a ray parallel to a
+    // — an unbounded one stays an every-ray prim. A cube's EPSILON-parallel hits lie outside its box: see CubeDir. Cones are never admitted: for a ray parallel to a
     // cone half (|a| < EPSILON) the reference emits t = -c/2·b without the y-limit test (cone.rs:100-108),
     // a hit that can lie anywhere along the ray, so no box bounds a cone's intersections.
     double r = 1.0, y0 = -1.0, y1 = 1.0;
@@ -524,6 +541,79 @@ inline void fill_recs(const rtc_scene_desc* d, AccelBuild& A) {
   }
 }
 
+// Face families of the scene's cubes (see CubeDir). Returns false when there are more than CUBE_DIR_MAX, or a
+// transform is unusable: the cubes then stay every-ray prims.
+inline bool cube_face_families(const rtc_scene_desc* d, AccelBuild& A) {
+  A.n_cube_dirs = 0;
+  std::vector<char> seen(d->n_xforms, 0);
+  for (uint32_t i = 0; i < d->n_nodes; i++) {
+    const rtc_node& nd = d->nodes[i];
+    if (nd.kind != RTC_CUBE || seen[(size_t)nd.xform]) continue;
+    seen[(size_t)nd.xform] = 1;
+    const double* inv = d->xforms + 12 * (size_t)nd.xform;
+    for (int r = 0; r < 3; r++) {
+      double u[3] = {inv[4 * r], inv[4 * r + 1], inv[4 * r + 2]};
+      const double len = std::sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
+      if (!(len > 0.0) || !std::isfinite(len)) return false;
+      for (int c = 0; c < 3; c++) u[c] /= len;
+      // canonical sign: the first component of magnitude above 1e-9 is positive
+      for (int c = 0; c < 3; c++) {
+        if (std::fabs(u[c]) > 1e-9) {
+          if (u[c] < 0.0) for (int k = 0; k < 3; k++) u[k] = -u[k];
+          break;
+        }
+      }
+      const double theta = 1e-5 / len;  // EPSILON, lib.rs:18
+      const double th2 = 2.0 * theta * theta * (1.0 + 1e-6);
+      if (!std::isfinite(th2)) return false;
+      int k = 0;
+      for (; k < A.n_cube_dirs; k++) {
+        const CubeDir& c = A.cube_dirs[k];
+        if (std::fabs(c.ux - u[0]) < 1e-13 && std::fabs(c.uy - u[1]) < 1e-13 && std::fabs(c.uz - u[2]) < 1e-13) break;
+      }
+      if (k < A.n_cube_dirs) {
+        A.cube_dirs[k].th2 = std::max(A.cube_dirs[k].th2, th2);
+      } else {
+        if (A.n_cube_dirs >= CUBE_DIR_MAX) { A.n_cube_dirs = 0; return false; }
+        A.cube_dirs[A.n_cube_dirs++] = CubeDir{u[0], u[1], u[2], th2};
+      }
+    }
+  }
+  return true;
+}
+
+// BVH_CUBE_BIT on every child reference whose subtree holds a cube (after Builder::build; leaf ranges are already
+// shifted by the always-prefix).
+inline void mark_cube_subtrees(AccelBuild& A) {
+  if (A.bvh.empty() || A.n_cube_dirs == 0) return;
+  std::vector<signed char> memo(A.bvh.size(), -1);
+  auto leaf_has = [&](int32_t c, int32_t n) {
+    for (int32_t k = c; k < c + n; k++)
+      if ((A.leaf_recs[(size_t)(k - A.n_always)].kind_flags >> 24) == (uint32_t)RTC_CUBE) return true;
+    return false;
+  };
+  // iterative post-order (depth is bounded, but a million-node tree should not recurse on the host stack)
+  std::vector<int32_t> stack{0};
+  while (!stack.empty()) {
+    const int32_t i = stack.back();
+    BvhNode& nd = A.bvh[(size_t)i];
+    bool ready = true;
+    if (nd.n0 == 0 && memo[(size_t)nd.c0] < 0) { stack.push_back(nd.c0); ready = false; }
+    if (nd.n1 == 0 && memo[(size_t)nd.c1] < 0) { stack.push_back(nd.c1); ready = false; }
+    if (!ready) continue;
+    stack.pop_back();
+    const bool h0 = nd.n0 > 0 ? leaf_has(nd.c0, nd.n0) : (nd.n0 == 0 ? memo[(size_t)nd.c0] > 0 : false);
+    const bool h1 = nd.n1 > 0 ? leaf_has(nd.c1, nd.n1) : (nd.n1 == 0 ? memo[(size_t)nd.c1] > 0 : false);
+    memo[(size_t)i] = (h0 || h1) ? 1 : 0;
+  }
+  for (BvhNode& nd : A.bvh) {
+    const bool h0 = nd.n0 > 0 ? leaf_has(nd.c0, nd.n0) : (nd.n0 == 0 ? memo[(size_t)nd.c0] > 0 : false);
+    const bool h1 = nd.n1 > 0 ? leaf_has(nd.c1, nd.n1) : (nd.n1 == 0 ? memo[(size_t)nd.c1] > 0 : false);
+    if (h0) nd.c0 |= BVH_CUBE_BIT;
+    if (h1) nd.c1 |= BVH_CUBE_BIT;
+  }
+}
+
 // `d` must already be structurally valid (rtc_api.cu validate()).
 inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
   using namespace accel_detail;
@@ -536,6 +626,7 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
   A.leaf_recs.clear();
   std::vector<Prim> cand;
   FwdCache fwd_cache(d->n_xforms);
+  const bool cubes_ok = cube_face_families(d, A);
   struct Open { int32_t end, node; };
   std::vector<Open> groups;
   int32_t i = 0;
@@ -552,7 +643,7 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
     } else {
       Prim p;
       p.node = i;
-      if (nd.kind != RTC_PLANE && leaf_world_box(d, nd, p.box, fwd_cache)) {
+      if (nd.kind != RTC_PLANE && leaf_world_box(d, nd, p.box, fwd_cache, cubes_ok)) {
         for (int a = 0; a < 3; a++) p.c[a] = 0.5 * (p.box.lo[a] + p.box.hi[a]);
         cand.push_back(p);
       } else {
@@ -589,6 +680,7 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
     for (auto& p : cand) A.prims.push_back(p.node);
     std::sort(A.prims.begin(), A.prims.end());
     A.n_always = (int32_t)A.prims.size();
+    A.n_cube_dirs = 0;
     fill_recs(d, A);
     return;
   }
@@ -597,6 +689,7 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
   const auto t1 = std::chrono::steady_clock::now();
   Builder b(cand, A, d);
   b.build();
+  mark_cube_subtrees(A);
   if (std::getenv("RTC_TIMING")) {
     const auto t2 = std::chrono::steady_clock::now();
     std::fprintf(stderr, "build_accel: walk+boxes+parents %.1f ms, BVH over %zu prims %.1f ms (%d threads)\n",

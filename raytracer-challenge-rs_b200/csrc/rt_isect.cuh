@@ -38,6 +38,9 @@ struct SceneView {
   int32_t n_sph, n_pl;       // always-prefix: [0,n_sph) spheres, [n_sph,n_sph+n_pl) planes, then the rest
   int32_t sane_indices;      // 1: every material's refractive_index is finite and > 0 (schlick() is then finite)
   SphCull sph_cull[SPH_CULL_MAX];  // bounding spheres of the first every-ray spheres (parameter bank)
+  CubeDir cube_dirs[CUBE_DIR_MAX]; // face families of the cubes in the BVH (EPSILON-parallel rule of cube.rs:30-48)
+  int32_t n_cube_dirs;
+  int32_t _pad_cube;
 };
 
 RTC_HD void slab_axis(double origin, double direction, double mn, double mx, double& tmin, double& tmax) {

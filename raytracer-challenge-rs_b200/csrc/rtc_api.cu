@@ -587,6 +587,8 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   v.n_sph = accel.n_sph;
   v.n_pl = accel.n_pl;
   for (int k = 0; k < SPH_CULL_MAX; k++) v.sph_cull[k] = accel.sph_cull[k];
+  for (int k = 0; k < CUBE_DIR_MAX; k++) v.cube_dirs[k] = accel.cube_dirs[k];
+  v.n_cube_dirs = accel.n_cube_dirs;
   v.n_bvh = (int32_t)accel.bvh.size();
   v.n_nodes = (int32_t)d->n_nodes;
   v.n_lights = (int32_t)d->n_lights;

@@ -43,6 +43,8 @@ void build_view(const rtc_scene_desc* d, Built& b) {
   v.parent = b.accel.parent.data(); v.prims = b.accel.prims.data(); v.recs = b.accel.recs.data(); v.leaf_recs = b.accel.leaf_recs.data();
   v.bvh = b.accel.bvh.data(); v.n_always = b.accel.n_always; v.n_sph = b.accel.n_sph; v.n_pl = b.accel.n_pl; v.n_bvh = (int32_t)b.accel.bvh.size();
   for (int k = 0; k < SPH_CULL_MAX; k++) v.sph_cull[k] = b.accel.sph_cull[k];
+  for (int k = 0; k < CUBE_DIR_MAX; k++) v.cube_dirs[k] = b.accel.cube_dirs[k];
+  v.n_cube_dirs = b.accel.n_cube_dirs;
 }
 CameraD make_cam(const rtc_camera* c) {
   CameraD cam;

@@ -163,3 +163,71 @@ def test_overflow_is_reported_by_kernel_source(pkg, prod, emul):
     rgb, t = np.zeros_like(o), np.zeros(1)
     err = emul.lib.emul_trace_rays(C.byref(flat.desc), 1, o.ctypes.data, d.ctypes.data, 1, rgb.ctypes.data, t.ctypes.data)
     assert err & 1                                         # ERR_OVERFLOW
+
+
+def cube_grazing_world(api, pkg, rotated=False):
+    """A unit cube plus nine far cubes (enough boundable prims for a BVH). Cube::check_axis (cube.rs:30-48) calls an
+    object-space direction component below EPSILON parallel and then decides by the ORIGIN alone, so a ray starting
+    inside the x-slab with 0 < dx < 1e-5 'hits' the cube although its exact path has left the slab: a hit outside any
+    box around the cube."""
+    T = pkg.transform
+    w = api.world()
+    w.add_light((-10, 10, -10), (1, 1, 1))
+    rot = T.rotation_y(0.3) if rotated else T.translation(0, 0, 0)
+    w.add_object(api.cube().set_transform(rot).set_material(pkg.Material(color=(0.9, 0.3, 0.2), reflective=0.2)))
+    for k in range(9):
+        w.add_object(api.cube().set_transform(T.chain(T.scaling(0.5, 0.5, 0.5), rot, T.translation(40.0 + 3.0 * k, 5.0, 30.0)))
+                     .set_material(pkg.Material(color=(0.2, 0.3 + 0.05 * k, 0.9))))
+    return w
+
+
+def grazing_camera(api, pkg, n, rotated=False):
+    import math
+    T = pkg.transform
+    c = api.camera(n, n, 6e-5)   # directions span dx in about +-3e-5: both sides of EPSILON
+    if rotated:
+        ca, sa = math.cos(0.3), math.sin(0.3)
+        # the unrotated set-up turned with the cube: origin just inside the x-slab in object space
+        o = (0.99999 * ca + -5.0 * sa, 0.3, -0.99999 * sa + -5.0 * ca)
+        t = (0.99999 * ca + 0.0 * sa, 0.3, -0.99999 * sa + 0.0 * ca)
+    else:
+        o, t = (0.99999, 0.3, -5.0), (0.99999, 0.3, 0.0)
+    c.set_transform(T.view_transform(o, t, (0, 1, 0)))
+    return c
+
+
+@pytest.mark.parametrize("rotated", [False, True])
+def test_cube_epsilon_parallel_hits_survive_the_bvh_kernel_source(pkg, prod, orc, emul, rotated):
+    want, iw = orc.render(grazing_camera(orc.api, pkg, 24, rotated), cube_grazing_world(orc.api, pkg, rotated), threads=0)
+    wp, cp = cube_grazing_world(prod, pkg, rotated), grazing_camera(prod, pkg, 24, rotated)
+    flat = pkg.FlatScene(wp)
+    a, ia = emul.render(cp, wp, flat=flat, faithful=True)
+    b, ib = emul.render(cp, wp, flat=flat, faithful=False)
+    assert np.array_equal(a, want) and ia["rays"] == iw["rays"]
+    assert np.array_equal(b, want) and ib["rays"] == iw["rays"]
+    lit = np.sum(np.any(want > 0, axis=-1))
+    assert 0 < lit                                    # the quirk's hits are in the frame
+    # the advisor's single ray: 1x1 camera at (0.999999, 0, -5) looking along (5e-6, 0, 1)
+    if not rotated:
+        for api_, rend in ((orc.api, None), (prod, emul)):
+            c1 = api_.camera(1, 1, 0.1)
+            c1.set_transform(pkg.transform.view_transform((0.999999, 0, -5), (0.999999 + 5e-6, 0, -4), (0, 1, 0)))
+            w1 = cube_grazing_world(api_, pkg)
+            if rend is None:
+                w0, i0 = orc.render(c1, w1, threads=0)
+            else:
+                g0, j0 = emul.render(c1, w1, faithful=False)
+        assert np.array_equal(g0, w0) and j0["rays"] == i0["rays"] and i0["rays"] >= 2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("rotated", [False, True])
+def test_cube_epsilon_parallel_hits_survive_the_bvh_gpu(pkg, prod, orc, rotated):
+    want, iw = orc.render(grazing_camera(orc.api, pkg, 48, rotated), cube_grazing_world(orc.api, pkg, rotated), threads=0)
+    ds = pkg.DeviceScene(pkg.FlatScene(cube_grazing_world(prod, pkg, rotated)))
+    cp = grazing_camera(prod, pkg, 48, rotated)
+    for kw in (dict(faithful=True), dict(faithful=False), dict(wavefront=True)):
+        got, st = ds.render(cp, **kw)
+        assert st.rays == iw["rays"], kw
+        assert np.max(np.abs(got - want)) <= 1e-12, kw
+    ds.close()
