@@ -202,6 +202,16 @@ RTC_API int rtc_render_rgb8(rtc_scene* scene, const rtc_camera* camera, const rt
 RTC_API int rtc_trace_rays(rtc_scene* scene, size_t n, const double* origins, const double* directions,
                    uint32_t remaining, double* rgb_out, double* t_out);
 
+/* No counterpart in the reference. rtc_trace_rays for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): the
+ * device staging of the batch is a file-scope static __device__ array (RTC_TRACE_STATIC_MAX rays x 10 doubles =
+ * 320 KB per GPU that loads the library, held until exit), so the call allocates nothing — no cudaMalloc, cudaFree or
+ * allocating library routine. n > RTC_TRACE_STATIC_MAX is rejected with RTC_ERR_INVALID. Results are bit-identical
+ * to rtc_trace_rays. All calls share the one array per GPU: calls that overlap on a GPU (two host threads) race. */
+#define RTC_TRACE_STATIC_MAX 4096
+RTC_API int rtc_trace_rays_static(rtc_scene* scene, size_t n, const double* origins, const double* directions,
+                                  uint32_t remaining, double* rgb_out, double* t_out);
+
 /* Debug / known-answer entry: Intersection::prepare_computations (geometry/intersection.rs:53)
  * for one host ray. out[20] = hit(0/1), t, point[3], normalv[3], over_point[3], under_point[3],
  * reflectv[3], n1, n2, inside. */

@@ -97,6 +97,7 @@ def cuda_lib():
         lib.rtc_quantize_device.argtypes = [C.c_int, pd, sz, pd, vp]
         lib.rtc_render_rgb8.argtypes = [vp, C.POINTER(RtcCamera), C.POINTER(RtcOpts), pd, C.POINTER(RtcStats)]
         lib.rtc_trace_rays.argtypes = [vp, sz, pd, pd, u32, pd, pd]
+        lib.rtc_trace_rays_static.argtypes = [vp, sz, pd, pd, u32, pd, pd]
         lib.rtc_probe_hit.argtypes = [vp, pd, pd, pd]
         lib.rtc_is_shadowed.argtypes = [vp, pd, u32]
         lib.rtc_canvas_create.argtypes = [C.c_int, sz, C.POINTER(vp)]
@@ -259,13 +260,14 @@ class DeviceScene:
         _check(cuda_lib().rtc_scene_finish(self.h, stream, C.byref(st)))
         return st
 
-    def trace_rays(self, origins, directions, remaining=5):
+    def trace_rays(self, origins, directions, remaining=5, static=False):
+        """World::color_at for a ray batch; static=True goes through rtc_trace_rays_static (no allocation)."""
         o = np.ascontiguousarray(origins, dtype=np.float64).reshape(-1, 3)
         d = np.ascontiguousarray(directions, dtype=np.float64).reshape(-1, 3)
         rgb = np.zeros_like(o)
         t = np.zeros(o.shape[0], dtype=np.float64)
-        _check(cuda_lib().rtc_trace_rays(self.h, o.shape[0], o.ctypes.data, d.ctypes.data, remaining,
-                                         rgb.ctypes.data, t.ctypes.data))
+        fn = cuda_lib().rtc_trace_rays_static if static else cuda_lib().rtc_trace_rays
+        _check(fn(self.h, o.shape[0], o.ctypes.data, d.ctypes.data, remaining, rgb.ctypes.data, t.ctypes.data))
         return rgb, t
 
     def probe_hit(self, origin, direction):

@@ -452,6 +452,32 @@ struct CanvasPool {
 };
 CanvasPool g_canvas_pool;
 
+// rtc_trace_rays_static: device staging for a ray batch without any allocation. One file-scope array per GPU that
+// loads the library (320 KB, held until exit): [origins 3n | directions 3n | rgb 3n | t n] at RTC_TRACE_STATIC_MAX.
+// In host code `g_trace_scratch` is only the symbol's host-side stand-in; the device address is looked up once per
+// device with that device current (cudaGetSymbolAddress) and cached here.
+static __device__ __align__(256) double g_trace_scratch[(size_t)RTC_TRACE_STATIC_MAX * 10];
+struct TraceScratchTable {
+  std::mutex mu;
+  double* ptr[64] = {nullptr};
+  int get(int device, double** out) {
+    if (device < 0 || device >= 64) return fail(RTC_ERR_INVALID, "device index beyond the static scratch table (64)");
+    std::lock_guard<std::mutex> g(mu);
+    if (!ptr[device]) {
+      int cur = -1;
+      CUDA_TRY(cudaGetDevice(&cur));
+      if (cur != device) return fail(RTC_ERR_CUDA, "static scratch set-up needs its device current");
+      double* p = nullptr;
+      CUDA_TRY(cudaGetSymbolAddress((void**)&p, g_trace_scratch));
+      if (!p) return fail(RTC_ERR_CUDA, "cudaGetSymbolAddress(g_trace_scratch) returned NULL");
+      ptr[device] = p;
+    }
+    *out = ptr[device];
+    return RTC_OK;
+  }
+};
+TraceScratchTable g_trace_scratch_table;
+
 }  // namespace
 
 extern "C" {
@@ -822,6 +848,39 @@ int rtc_trace_rays(rtc_scene* s, size_t n, const double* origins, const double* 
   cleanup();
 #undef TRY_OR_CLEAN
   return rc;
+}
+
+// No counterpart in the reference: rtc_trace_rays for callers that must not allocate (CUDA graph capture around the
+// call site, tight serving loops). Same kernel, same stream, same counters; the staging lives in g_trace_scratch.
+// No cudaMalloc / cudaFree / allocating library call on this path. Every call shares the array: calls that overlap
+// on one GPU race (this one is synchronous, so only concurrent host threads can make them overlap).
+int rtc_trace_rays_static(rtc_scene* s, size_t n, const double* origins, const double* directions, uint32_t remaining,
+                          double* rgb_out, double* t_out) {
+  if (!s || !origins || !directions) return fail(RTC_ERR_INVALID, "NULL argument");
+  if ((int)remaining + 1 > MAX_FRAMES) return fail(RTC_ERR_UNSUPPORTED, "remaining > 7");
+  if (n > (size_t)RTC_TRACE_STATIC_MAX)
+    return fail(RTC_ERR_INVALID, "rtc_trace_rays_static: n = " + std::to_string(n) + " exceeds RTC_TRACE_STATIC_MAX = " +
+                                     std::to_string((int)RTC_TRACE_STATIC_MAX) + " rays (use rtc_trace_rays, or split the batch)");
+  if (n == 0) return RTC_OK;
+  CUDA_TRY(cudaSetDevice(s->device));
+  double* base = nullptr;
+  int rc = g_trace_scratch_table.get(s->device, &base);
+  if (rc) return rc;
+  const size_t cap = (size_t)RTC_TRACE_STATIC_MAX;
+  double *d_o = base, *d_d = base + 3 * cap, *d_rgb = base + 6 * cap, *d_t = base + 9 * cap;
+  CUDA_TRY(cudaMemcpyAsync(d_o, origins, 3 * n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  CUDA_TRY(cudaMemcpyAsync(d_d, directions, 3 * n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  // the array keeps the previous call's results: the kernel overwrites rgb/t of every ray < n, and the rest is
+  // never copied out; cleared all the same so that a faulting launch cannot hand back stale colours
+  CUDA_TRY(cudaMemsetAsync(d_rgb, 0, 4 * cap * sizeof(double), s->stream));
+  CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, N_COUNTERS * sizeof(unsigned long long), s->stream));
+  unsigned blocks = (unsigned)((n + 127) / 128);
+  if (s->has_csg) trace_kernel<true><<<blocks, 128, 0, s->stream>>>(s->view, n, d_o, d_d, (int)remaining, d_rgb, d_t, s->d_counters);
+  else trace_kernel<false><<<blocks, 128, 0, s->stream>>>(s->view, n, d_o, d_d, (int)remaining, d_rgb, d_t, s->d_counters);
+  CUDA_TRY(cudaGetLastError());
+  if (rgb_out) CUDA_TRY(cudaMemcpyAsync(rgb_out, d_rgb, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  if (t_out) CUDA_TRY(cudaMemcpyAsync(t_out, d_t, n * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  return read_counters(s, s->stream, nullptr);
 }
 
 int rtc_probe_hit(rtc_scene* s, const double* o, const double* dir, double* out20) {
