@@ -146,6 +146,8 @@ typedef struct rtc_opts {
                                          color_at call; aa_samples == 1 only) ...                          */
 #define RTC_OPT_RECURSIVE 8u          /* ... or the one-thread-per-pixel kernel; neither: the library picks.
                                          Both produce the same bits. */
+#define RTC_OPT_WAVE_LEVELS 16u       /* with the wavefront: 1 + 2 * max_depth level-synchronous passes (rt_wave.cuh) instead of
+                                         the one barrier-free persistent launch (rt_stream.cuh); same bits */
 #define RTC_OPT_AVERAGE 2u            /* render_multithreaded semantics even for aa_samples == 1:
                                          Color::average = (0 + c) * (1.0/1) (camera.rs:186) */
 
@@ -156,8 +158,15 @@ typedef struct rtc_stats {
   double kernel_ms;        /* render kernel(s), CUDA events on the launch stream */
   double total_ms;         /* whole call, incl. copies, host clock */
   uint32_t launches;       /* kernels launched by this call */
-  uint32_t _pad;
+  uint32_t flags;          /* RTC_STAT_* */
 } rtc_stats;
+
+#define RTC_STAT_WAVEFRONT 1u     /* the frame was rendered by a wavefront renderer */
+#define RTC_STAT_WAVE_FALLBACK 2u /* ... whose queues overflowed: rtc_scene_finish (or the synchronous entry points) rendered
+                                     the frame again with the recursive kernel. A caller that copied or pushed the canvas
+                                     between rtc_render_device and rtc_scene_finish must do so again. */
+#define RTC_STAT_WAVE_OVERFLOWED 4u /* some wavefront frame queued on this scene since the previous rtc_scene_finish overflowed
+                                     its queues (only the LAST frame is rendered again; earlier ones were left incomplete) */
 
 typedef struct rtc_scene rtc_scene;
 
@@ -235,6 +244,19 @@ RTC_API int rtc_canvas_download(rtc_canvas* canvas, double* host, size_t offset_
 RTC_API int rtc_canvas_push_tiles(rtc_canvas* canvas, const double* local_dev, uint32_t hsize, uint32_t vsize,
                                   uint32_t tile_rows, uint32_t rank, uint32_t nranks, void* stream);
 RTC_API void rtc_canvas_destroy(rtc_canvas* canvas);
+
+/* The HOST canvas of a multi-GPU render. What Camera::render_multithreaded hands back is the host Canvas its row
+ * blocks were gathered into (camera.rs:195-207); here that is ONE POSIX shared-memory segment (`name`, as for
+ * shm_open: "/something"), mapped by every rank's process and page-locked + mapped for that process's GPU
+ * (cudaHostRegisterPortable | cudaHostRegisterMapped). Every rank then calls
+ *     rtc_render(scene, camera, opts{rank, nranks, tile_rows}, rtc_host_canvas_ptr(canvas), stats)
+ * and ITS tiles reach the canvas over ITS OWN PCIe link (kernel stores straight into the mapping, or one strided DMA
+ * of the rank's tiles for the wavefront renderer) — N links instead of rank 0's one. `create` != 0: create and size the
+ * segment (rank 0; removed again by its rtc_host_canvas_destroy); 0: open an existing one. */
+typedef struct rtc_host_canvas rtc_host_canvas;
+RTC_API int rtc_host_canvas_create(const char* name, size_t n_doubles, int device, int create, rtc_host_canvas** out);
+RTC_API double* rtc_host_canvas_ptr(rtc_host_canvas* canvas);
+RTC_API void rtc_host_canvas_destroy(rtc_host_canvas* canvas);
 
 /* Debug / known-answer entry: Vector::normalize (vector.rs:25-28) of n host vectors (xyz triples) on
  * the device, through the same normalize() the kernels use (its divisions share one reciprocal). */

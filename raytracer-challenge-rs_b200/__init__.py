@@ -28,6 +28,10 @@ HOST_LIB = os.path.join(_HERE, "host", "librth_host.so")
 RTC_OPT_FAITHFUL_TRAVERSAL = 1
 RTC_OPT_AVERAGE = 2
 RTC_OPT_WAVEFRONT = 4
+RTC_OPT_WAVE_LEVELS = 16
+RTC_STAT_WAVEFRONT = 1
+RTC_STAT_WAVE_FALLBACK = 2
+RTC_STAT_WAVE_OVERFLOWED = 4
 RTC_OPT_RECURSIVE = 8
 
 
@@ -59,7 +63,7 @@ class RtcOpts(C.Structure):
 class RtcStats(C.Structure):
     _fields_ = [("rays_primary", C.c_uint64), ("rays_shadow", C.c_uint64), ("rays_reflect", C.c_uint64),
                 ("rays_refract", C.c_uint64), ("overflow_count", C.c_uint64), ("nan_count", C.c_uint64),
-                ("kernel_ms", C.c_double), ("total_ms", C.c_double), ("launches", C.c_uint32), ("_pad", C.c_uint32)]
+                ("kernel_ms", C.c_double), ("total_ms", C.c_double), ("launches", C.c_uint32), ("flags", C.c_uint32)]
 
     @property
     def rays(self):
@@ -67,6 +71,14 @@ class RtcStats(C.Structure):
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "_pad"}
+
+    @property
+    def wave_fallback(self):
+        return bool(self.flags & RTC_STAT_WAVE_FALLBACK)
+
+    @property
+    def wave_overflowed(self):
+        return bool(self.flags & RTC_STAT_WAVE_OVERFLOWED)
 
 
 class RtcError(RuntimeError):
@@ -109,6 +121,11 @@ def cuda_lib():
         lib.rtc_canvas_push_tiles.argtypes = [vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, vp]
         lib.rtc_canvas_destroy.argtypes = [vp]
         lib.rtc_canvas_destroy.restype = None
+        lib.rtc_host_canvas_create.argtypes = [C.c_char_p, sz, C.c_int, C.c_int, C.POINTER(vp)]
+        lib.rtc_host_canvas_ptr.argtypes = [vp]
+        lib.rtc_host_canvas_ptr.restype = vp
+        lib.rtc_host_canvas_destroy.argtypes = [vp]
+        lib.rtc_host_canvas_destroy.restype = None
         lib.rtc_measure_fp64.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double)]
         lib.rtc_debug_normalize.argtypes = [C.c_int, sz, pd, pd]
         _libs["cuda"] = lib
@@ -163,7 +180,8 @@ def _check(rc):
     return rc
 
 
-def make_opts(aa=1, max_depth=5, rows=None, tile_rows=8, rank=0, nranks=1, faithful=False, average=False, wavefront=None):
+def make_opts(aa=1, max_depth=5, rows=None, tile_rows=8, rank=0, nranks=1, faithful=False, average=False, wavefront=None,
+              wave_levels=False):
     o = RtcOpts()
     o.aa_samples, o.max_depth = aa, max_depth
     o.row_begin, o.row_end = (rows if rows else (0, 0))
@@ -171,6 +189,8 @@ def make_opts(aa=1, max_depth=5, rows=None, tile_rows=8, rank=0, nranks=1, faith
     o.flags = (RTC_OPT_FAITHFUL_TRAVERSAL if faithful else 0) | (RTC_OPT_AVERAGE if average else 0)
     if wavefront is not None:  # None: the library's default; True/False force one renderer (same bits either way)
         o.flags |= RTC_OPT_WAVEFRONT if wavefront else RTC_OPT_RECURSIVE
+    if wave_levels:    # the level-synchronous passes instead of the one barrier-free launch
+        o.flags |= RTC_OPT_WAVE_LEVELS
     return o
 
 

@@ -229,7 +229,7 @@ __global__ void __launch_bounds__(128, MINB) wave_forward_kernel(SceneView S, Ca
   }
 #endif
   flush_counters(rc, err, counters);
-  if (dropped) atomicAdd(counters + 6, (unsigned long long)dropped);
+  if (dropped) { atomicAdd(counters + 6, (unsigned long long)dropped); atomicAdd(counters + 7, 1ull); }
 }
 
 // shade_hit's last line (world.rs:62-67) for the suspended calls of one level.

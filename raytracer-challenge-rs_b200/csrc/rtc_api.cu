@@ -3,16 +3,23 @@
 //        -shared -o librtc_cuda.so rtc_api.cu
 // No CPU fallback: every compute entry point needs a CUDA device.
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstdio>
+#include <cerrno>
 #include <cstring>
 #include <mutex>
 #include <string>
 #include <vector>
 
-#include "rt_wave.cuh"
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include "rt_stream.cuh"
 
 using namespace rtk;
 
@@ -32,7 +39,8 @@ int fail(int code, const std::string& msg) {
     }                                                                                           \
   } while (0)
 
-constexpr int N_COUNTERS = 8;
+constexpr int N_COUNTERS = 8;       // what a frame resets and rtc_scene_finish reads
+constexpr int N_COUNTERS_ALLOC = 24;  // [8, 24): RTK_STREAM_STATS instrumentation (experiments)
 #ifndef RTK_WAVE_MIN_RANKS
 #define RTK_WAVE_MIN_RANKS 3
 #endif
@@ -58,13 +66,26 @@ struct rtc_scene {
   // the recursive kernel should a queue have overflowed
   char* wave_arena = nullptr;
   size_t wave_bytes = 0;
+  // streaming wavefront: the arena's child-colour slots hold sentinels for this (pixels, depth) layout; 0 = they do not
+  // (fresh or recycled arena, a level-synchronous frame, an abandoned frame): re-fill before the next streaming frame
+  size_t wave_clean_px = 0;
+  int wave_clean_depth = 0;
   bool lean = false;           // every-ray spheres and planes only: the kernels without BVH / generic leaf code
   bool tri_sph_only = false;   // spheres/planes every ray + a BVH of triangles and spheres: no generic leaf code
   bool has_branching = false;  // some material reflects AND refracts: shade_hit spawns two children, the tree grows as 2^depth
   bool last_wave = false;
+  uint32_t stat_flags = 0;     // RTC_STAT_* of the frame in flight
   CameraD last_cam{};
   RenderParams last_P{};
   double* last_out = nullptr;
+};
+
+struct rtc_host_canvas {
+  std::string name;
+  double* ptr = nullptr;
+  size_t bytes = 0;
+  int device = 0;
+  bool creator = false, registered = false;
 };
 
 struct rtc_canvas {
@@ -138,6 +159,18 @@ int read_counters(rtc_scene* s, cudaStream_t stream, rtc_stats* stats) {
   unsigned long long h[N_COUNTERS];
   CUDA_TRY(cudaMemcpyAsync(h, s->d_counters, sizeof h, cudaMemcpyDeviceToHost, stream));
   CUDA_TRY(cudaStreamSynchronize(stream));
+#if defined(RTK_STREAM_STATS)
+  if (s->stat_flags & RTC_STAT_WAVEFRONT) {
+    unsigned long long d[16];
+    CUDA_TRY(cudaMemcpy(d, s->d_counters + 8, sizeof d, cudaMemcpyDeviceToHost));
+    std::fprintf(stderr, "stream stats: batches %llu items %llu idle polls %llu | clocks/warp-sum: acquire %llu stamp-wait %llu work %llu | stamp spins %llu partial batches %llu CAS failures %llu\n",
+                 d[0], d[1], d[2], d[3], d[4], d[5], d[6], d[7], d[8]);
+  }
+#endif
+  if (h[7]) {
+    s->stat_flags |= RTC_STAT_WAVE_OVERFLOWED;
+    CUDA_TRY(cudaMemsetAsync(s->d_counters + 7, 0, sizeof(unsigned long long), stream));
+  }
   if (stats) {
     stats->rays_primary = h[0]; stats->rays_shadow = h[1]; stats->rays_reflect = h[2]; stats->rays_refract = h[3];
     stats->overflow_count = h[4]; stats->nan_count = h[5];
@@ -257,23 +290,29 @@ struct ArenaPool {
   std::mutex mu;
   char* ptr[16] = {nullptr};
   size_t bytes[16] = {0};
-  char* take(int dev, size_t need, size_t& got) {
+  size_t clean_px[16] = {0};
+  int clean_depth[16] = {0};
+  char* take(int dev, size_t need, size_t& got, size_t& cpx, int& cdepth) {
     std::lock_guard<std::mutex> g(mu);
     if (dev >= 0 && dev < 16 && ptr[dev] && bytes[dev] >= need) {
       char* p = ptr[dev];
       got = bytes[dev];
+      cpx = clean_px[dev];
+      cdepth = clean_depth[dev];
       ptr[dev] = nullptr;
       bytes[dev] = 0;
       return p;
     }
     return nullptr;
   }
-  void give(int dev, char* p, size_t n) {
+  void give(int dev, char* p, size_t n, size_t cpx, int cdepth) {
     {
       std::lock_guard<std::mutex> g(mu);
       if (dev >= 0 && dev < 16 && bytes[dev] < n) {
         std::swap(ptr[dev], p);
         std::swap(bytes[dev], n);
+        clean_px[dev] = cpx;
+        clean_depth[dev] = cdepth;
       }
     }
     if (p) cudaFree(p);
@@ -283,16 +322,22 @@ ArenaPool g_arena_pool;
 
 int ensure_arena(rtc_scene* s, size_t need) {
   if (s->wave_bytes >= need) return RTC_OK;
-  if (s->wave_arena) g_arena_pool.give(s->device, s->wave_arena, s->wave_bytes);
+  if (s->wave_arena) g_arena_pool.give(s->device, s->wave_arena, s->wave_bytes, s->wave_clean_px, s->wave_clean_depth);
   s->wave_arena = nullptr;
   s->wave_bytes = 0;
+  s->wave_clean_px = 0;
+  s->wave_clean_depth = 0;
   size_t got = 0;
-  s->wave_arena = g_arena_pool.take(s->device, need, got);
+  s->wave_arena = g_arena_pool.take(s->device, need, got, s->wave_clean_px, s->wave_clean_depth);
   if (s->wave_arena) {
     s->wave_bytes = got;
   } else {
     CUDA_TRY(cudaMalloc((void**)&s->wave_arena, need));
     s->wave_bytes = need;
+    // the streaming wavefront reads ready stamps out of queue slots nobody has written yet: start from zero
+    // (epochs are never 0); a recycled arena only holds stamps of earlier, different epochs
+    CUDA_TRY(cudaMemsetAsync(s->wave_arena, 0, need, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
   }
   return RTC_OK;
 }
@@ -326,6 +371,7 @@ int launch_wave(rtc_scene* s, const CameraD& cam, const RenderParams& P, double*
   }
   int rc = ensure_arena(s, off);
   if (rc) return rc;
+  s->wave_clean_px = 0;  // these passes leave colours in the child slots
   char* base = s->wave_arena;
   unsigned long long* n_items = (unsigned long long*)base;  // [0,128): u64 per level (front | rear << 32)
   uint32_t* n_recs = (uint32_t*)(base + 128);               // [128,192)
@@ -370,6 +416,70 @@ int launch_wave(rtc_scene* s, const CameraD& cam, const RenderParams& P, double*
   return RTC_OK;
 }
 
+std::atomic<uint32_t> g_wave_epoch{1};
+
+// The same wavefront as ONE persistent launch without level barriers (rt_stream.cuh).
+int launch_stream(rtc_scene* s, const CameraD& cam, const RenderParams& P, double* out, cudaStream_t stream) {
+  const int D = P.max_depth;
+  const size_t px = (size_t)P.owned_rows * cam.hsize;
+  if (px == 0) return RTC_OK;
+  if (px > 0x3fffffffu) return fail(RTC_ERR_UNSUPPORTED, "frame too large for the wavefront queues");
+  size_t off = STREAM_CTRL_BYTES;  // the control block (rt_stream.cuh: one word per 128-byte line)
+  StreamArgs A{};
+  struct Lay { size_t items, recs, child; } lay[WAVE_MAX_LEVELS + 1] = {};
+  for (int L = 0; L <= D; L++) {
+    A.lv[L].cap_items = L == 0 ? 0u : (uint32_t)(2 * px);
+    A.lv[L].cap_recs = L == D ? 0u : (L == 0 ? (uint32_t)px : (uint32_t)(2 * px));
+    lay[L].items = off; off += align_up((size_t)A.lv[L].cap_items * sizeof(WaveItem));
+    lay[L].recs = off; off += align_up((size_t)A.lv[L].cap_recs * sizeof(WaveRec));
+    lay[L].child = off; off += align_up((size_t)A.lv[L].cap_recs * 6 * sizeof(double));
+  }
+  int rc = ensure_arena(s, off);
+  if (rc) return rc;
+  char* base = s->wave_arena;
+  for (int L = 0; L <= D; L++) {
+    A.lv[L].items = (WaveItem*)(base + lay[L].items);
+    A.lv[L].recs = (WaveRec*)(base + lay[L].recs);
+    A.lv[L].child = (double*)(base + lay[L].child);
+  }
+  if (s->wave_clean_px != px || s->wave_clean_depth != D) {
+    // child colour slots start as sentinels ("nothing delivered"); a frame that completes leaves them that way
+    for (int L = 0; L < D; L++) {
+      const size_t n = (size_t)A.lv[L].cap_recs * 6;
+      if (n) wave_fill_kernel<<<s->sm_count * 8, 256, 0, stream>>>((unsigned long long*)A.lv[L].child, n, WAVE_SENTINEL);
+    }
+    CUDA_TRY(cudaGetLastError());
+    s->wave_clean_px = px;
+    s->wave_clean_depth = D;
+  }
+  A.ctrl = base;
+  A.max_depth = D;
+  uint32_t e = g_wave_epoch.fetch_add(1) & 0x7fffffffu;
+  if (e == 0) e = g_wave_epoch.fetch_add(1) & 0x7fffffffu;
+  A.epoch = e;
+  CUDA_TRY(cudaMemsetAsync(base, 0, STREAM_CTRL_BYTES, stream));
+#if defined(RTK_STREAM_STATS)
+  CUDA_TRY(cudaMemsetAsync(s->d_counters + 8, 0, 16 * sizeof(unsigned long long), stream));
+#endif
+  const int minb = s->big_accel ? 8 : RTK_MIN_BLOCKS;
+  const int grid = s->sm_count * minb;
+  if (s->has_csg) {
+    if (s->big_accel) wave_stream_kernel<true, 8><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+    else wave_stream_kernel<true, RTK_MIN_BLOCKS><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+  } else if (s->lean) {
+    wave_stream_kernel<false, RTK_MIN_BLOCKS, 2><<<s->sm_count * RTK_MIN_BLOCKS, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+  } else if (s->tri_sph_only) {
+    if (s->big_accel) wave_stream_kernel<false, 8, 4><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+    else wave_stream_kernel<false, RTK_MIN_BLOCKS, 4><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+  } else {
+    if (s->big_accel) wave_stream_kernel<false, 8><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+    else wave_stream_kernel<false, RTK_MIN_BLOCKS><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+  }
+  s->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return RTC_OK;
+}
+
 // RTC_WAVEFRONT=0/1 in the environment overrides the choice (experiments); otherwise RTC_OPT_WAVEFRONT /
 // RTC_OPT_RECURSIVE in rtc_opts.flags, otherwise the measured default.
 // Default (measured, profiles/r01h_shard_probe.log, r01k_ncu_teapot_summary.md): on a whole frame the recursive kernel
@@ -391,13 +501,18 @@ bool use_wavefront(const rtc_scene* s, const RenderParams& P, bool faithful, uin
 }
 
 int launch_frame(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool faithful, double* out, cudaStream_t stream) {
-  CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, N_COUNTERS * sizeof(unsigned long long), stream));
+  // counters[7] is sticky: wavefront frames whose queues overflowed since the last rtc_scene_finish
+  CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, (N_COUNTERS - 1) * sizeof(unsigned long long), stream));
   CUDA_TRY(cudaEventRecord(s->ev0, stream));
   s->last_wave = use_wavefront(s, P, faithful, P.flags);
+  s->stat_flags = s->last_wave ? RTC_STAT_WAVEFRONT : 0u;
   int rc;
   if (s->last_wave) {
     s->last_cam = cam; s->last_P = P; s->last_out = out;
-    rc = launch_wave(s, cam, P, out, stream);
+    // one barrier-free persistent launch (rt_stream.cuh) unless the level-synchronous passes are asked for
+    static const char* env_levels = std::getenv("RTC_WAVE_LEVELS");
+    const bool levels = env_levels ? env_levels[0] == '1' : (P.flags & RTC_OPT_WAVE_LEVELS) != 0;
+    rc = levels ? launch_wave(s, cam, P, out, stream) : launch_stream(s, cam, P, out, stream);
   } else {
     rc = launch_rows(s, cam, P, faithful, out, stream, 0, 0);
   }
@@ -415,7 +530,9 @@ int resolve_wave(rtc_scene* s, cudaStream_t stream) {
   CUDA_TRY(cudaMemcpyAsync(&dropped, s->d_counters + 6, sizeof dropped, cudaMemcpyDeviceToHost, stream));
   CUDA_TRY(cudaStreamSynchronize(stream));
   if (!dropped) return RTC_OK;
-  CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, N_COUNTERS * sizeof(unsigned long long), stream));
+  s->stat_flags |= RTC_STAT_WAVE_FALLBACK;
+  s->wave_clean_px = 0;  // the abandoned frame left colours in child slots
+  CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, (N_COUNTERS - 1) * sizeof(unsigned long long), stream));
   CUDA_TRY(cudaEventRecord(s->ev0, stream));
   int rc = launch_rows(s, s->last_cam, s->last_P, false, s->last_out, stream, 0, 0);
   if (rc) return rc;
@@ -564,10 +681,10 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   }
   if ((e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
   { int n = 0; if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && n > 0) s->sm_count = n; }
-  const size_t tail = align_up(N_COUNTERS * sizeof(unsigned long long)) + align_up(32 * sizeof(double));
+  const size_t tail = align_up(N_COUNTERS_ALLOC * sizeof(unsigned long long)) + align_up(32 * sizeof(double));
   if ((e = cudaMallocAsync((void**)&s->slab, total + tail, s->stream)) != cudaSuccess) return bail(e, "cudaMallocAsync(scene)");
   s->d_counters = (unsigned long long*)(s->slab + total);
-  s->d_probe = (double*)(s->slab + total + align_up(N_COUNTERS * sizeof(unsigned long long)));
+  s->d_probe = (double*)(s->slab + total + align_up(N_COUNTERS_ALLOC * sizeof(unsigned long long)));
   if ((e = cudaEventCreate(&s->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
   if ((e = cudaEventCreate(&s->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
   const auto t_built = std::chrono::steady_clock::now();
@@ -639,7 +756,7 @@ void rtc_scene_destroy(rtc_scene* s) {
     if (s->stream) cudaFreeAsync(s->slab, s->stream); else cudaFree(s->slab);
   }
   if (s->d_canvas) g_canvas_pool.give(s->device, s->d_canvas, s->canvas_doubles);
-  if (s->wave_arena) g_arena_pool.give(s->device, s->wave_arena, s->wave_bytes);
+  if (s->wave_arena) g_arena_pool.give(s->device, s->wave_arena, s->wave_bytes, s->wave_clean_px, s->wave_clean_depth);
   if (s->ev0) cudaEventDestroy(s->ev0);
   if (s->ev1) cudaEventDestroy(s->ev1);
   if (s->stream) cudaStreamDestroy(s->stream);
@@ -682,6 +799,7 @@ int rtc_scene_finish(rtc_scene* s, void* stream_, rtc_stats* stats) {
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, s->ev0, s->ev1) == cudaSuccess) stats->kernel_ms = ms; else cudaGetLastError();
     stats->launches = s->launches;
+    stats->flags = s->stat_flags;
   }
   return rc;
 }
@@ -753,13 +871,29 @@ int rtc_render(rtc_scene* s, const rtc_camera* camera, const rtc_opts* opts, dou
     rc = resolve_wave(s, s->stream);  // before the canvas is read
     if (rc) return rc;
     // device → host: only the rows this call rendered (owned tiles clipped to the row range)
-    for (uint32_t t = P.rank; (size_t)t * P.tile_rows < cam.vsize; t += P.nranks) {
-      uint32_t y0 = t * P.tile_rows, y1 = y0 + P.tile_rows;
-      if (y0 < P.row_begin) y0 = P.row_begin;
-      if (y1 > P.row_end) y1 = P.row_end;
-      if (y0 >= y1) continue;
-      size_t off = (size_t)y0 * row_doubles, cnt = (size_t)(y1 - y0) * row_doubles;
-      CUDA_TRY(cudaMemcpyAsync(rgb_host + off, s->d_canvas + off, cnt * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+    if (P.row_begin == 0 && P.row_end == cam.vsize) {
+      // whole frame: this rank's whole tiles leave as ONE strided DMA (plus the ragged last tile if it is ours)
+      const size_t row_bytes = row_doubles * sizeof(double), tile_bytes = row_bytes * P.tile_rows;
+      const uint32_t full_tiles = cam.vsize / P.tile_rows;
+      const uint32_t mine = full_tiles > P.rank ? (full_tiles - P.rank + P.nranks - 1) / P.nranks : 0;
+      const size_t first = (size_t)P.rank * tile_bytes;
+      if (mine)
+        CUDA_TRY(cudaMemcpy2DAsync((char*)rgb_host + first, tile_bytes * P.nranks, (const char*)s->d_canvas + first,
+                                   tile_bytes * P.nranks, tile_bytes, mine, cudaMemcpyDeviceToHost, s->stream));
+      if (cam.vsize % P.tile_rows && full_tiles % P.nranks == P.rank) {
+        const size_t off = (size_t)full_tiles * tile_bytes;
+        CUDA_TRY(cudaMemcpyAsync((char*)rgb_host + off, (const char*)s->d_canvas + off, row_bytes * (cam.vsize % P.tile_rows),
+                                 cudaMemcpyDeviceToHost, s->stream));
+      }
+    } else {
+      for (uint32_t t = P.rank; (size_t)t * P.tile_rows < cam.vsize; t += P.nranks) {
+        uint32_t y0 = t * P.tile_rows, y1 = y0 + P.tile_rows;
+        if (y0 < P.row_begin) y0 = P.row_begin;
+        if (y1 > P.row_end) y1 = P.row_end;
+        if (y0 >= y1) continue;
+        size_t off = (size_t)y0 * row_doubles, cnt = (size_t)(y1 - y0) * row_doubles;
+        CUDA_TRY(cudaMemcpyAsync(rgb_host + off, s->d_canvas + off, cnt * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+      }
     }
   }
   rtc_stats local;
@@ -976,6 +1110,48 @@ void rtc_canvas_destroy(rtc_canvas* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   if (c->opened) cudaIpcCloseMemHandle(c->ptr); else cudaFree(c->ptr);
+  delete c;
+}
+
+int rtc_host_canvas_create(const char* name, size_t n_doubles, int device, int create, rtc_host_canvas** out) {
+  if (!out || !name || name[0] != '/' || n_doubles == 0) return fail(RTC_ERR_INVALID, "bad host canvas (name must start with '/')");
+  *out = nullptr;
+  CUDA_TRY(cudaSetDevice(device));
+  const size_t bytes = n_doubles * sizeof(double);
+  int fd = shm_open(name, create ? (O_CREAT | O_RDWR) : O_RDWR, 0600);
+  if (fd < 0) return fail(RTC_ERR_INVALID, std::string("shm_open(") + name + "): " + std::strerror(errno));
+  if (create && ftruncate(fd, (off_t)bytes) != 0) {
+    const std::string m = std::string("ftruncate: ") + std::strerror(errno);
+    close(fd);
+    shm_unlink(name);
+    return fail(RTC_ERR_INVALID, m);
+  }
+  void* p = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+  close(fd);
+  if (p == MAP_FAILED) {
+    if (create) shm_unlink(name);
+    return fail(RTC_ERR_INVALID, std::string("mmap: ") + std::strerror(errno));
+  }
+  rtc_host_canvas* c = new rtc_host_canvas();
+  c->name = name; c->ptr = (double*)p; c->bytes = bytes; c->device = device; c->creator = create != 0;
+  if (create) std::memset(p, 0, bytes);  // touch every page before it is locked
+  cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped);
+  if (e != cudaSuccess) {
+    const std::string m = std::string("cudaHostRegister(host canvas): ") + cudaGetErrorString(e);
+    rtc_host_canvas_destroy(c);
+    return fail(RTC_ERR_CUDA, m);
+  }
+  c->registered = true;
+  *out = c;
+  return RTC_OK;
+}
+double* rtc_host_canvas_ptr(rtc_host_canvas* c) { return c ? c->ptr : nullptr; }
+void rtc_host_canvas_destroy(rtc_host_canvas* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->registered) cudaHostUnregister(c->ptr);
+  if (c->ptr) munmap(c->ptr, c->bytes);
+  if (c->creator) shm_unlink(c->name.c_str());
   delete c;
 }
 

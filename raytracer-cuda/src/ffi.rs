@@ -44,6 +44,10 @@ pub const RTC_OPT_FAITHFUL_TRAVERSAL: u32 = 1;
 pub const RTC_OPT_AVERAGE: u32 = 2;
 pub const RTC_OPT_WAVEFRONT: u32 = 4;
 pub const RTC_OPT_RECURSIVE: u32 = 8;
+pub const RTC_OPT_WAVE_LEVELS: u32 = 16;
+pub const RTC_STAT_WAVEFRONT: u32 = 1;
+pub const RTC_STAT_WAVE_FALLBACK: u32 = 2;
+pub const RTC_STAT_WAVE_OVERFLOWED: u32 = 4;
 
 pub const RTC_TRACE_STATIC_MAX: usize = 4096;
 
@@ -151,7 +155,7 @@ pub struct rtc_stats {
     pub kernel_ms: f64,
     pub total_ms: f64,
     pub launches: u32,
-    pub _pad: u32,
+    pub flags: u32,
 }
 
 /// Opaque handles.
@@ -161,6 +165,10 @@ pub struct rtc_scene {
 }
 #[repr(C)]
 pub struct rtc_canvas {
+    _private: [u8; 0],
+}
+#[repr(C)]
+pub struct rtc_host_canvas {
     _private: [u8; 0],
 }
 
@@ -186,6 +194,9 @@ extern "C" {
     pub fn rtc_canvas_download(canvas: *mut rtc_canvas, host: *mut f64, offset_doubles: usize, n_doubles: usize) -> c_int;
     pub fn rtc_canvas_push_tiles(canvas: *mut rtc_canvas, local_dev: *const f64, hsize: u32, vsize: u32, tile_rows: u32, rank: u32, nranks: u32, stream: *mut c_void) -> c_int;
     pub fn rtc_canvas_destroy(canvas: *mut rtc_canvas);
+    pub fn rtc_host_canvas_create(name: *const c_char, n_doubles: usize, device: c_int, create: c_int, out: *mut *mut rtc_host_canvas) -> c_int;
+    pub fn rtc_host_canvas_ptr(canvas: *mut rtc_host_canvas) -> *mut f64;
+    pub fn rtc_host_canvas_destroy(canvas: *mut rtc_host_canvas);
     pub fn rtc_debug_normalize(device: c_int, n: usize, xyz_host: *const f64, out_host: *mut f64) -> c_int;
     pub fn rtc_measure_fp64(device: c_int, fused: c_int, gflops_out: *mut f64) -> c_int;
 }

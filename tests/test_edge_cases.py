@@ -85,13 +85,13 @@ def test_big_accel_instantiations_match_oracle(case, pkg, prod, orc, monkeypatch
     monkeypatch.setenv("RTC_BIG_ACCEL", "1")
     wp, cp = scenes.CONFIGS[name](prod, **kw)
     ds = pkg.DeviceScene(pkg.FlatScene(wp))
-    for wavefront in (False, True):
-        got, st = ds.render(cp, aa=aa, wavefront=wavefront)
-        assert st.launches == (11 if wavefront else 1)
+    for kw, launches in ((dict(wavefront=False), 1), (dict(wavefront=True), 1), (dict(wavefront=True, wave_levels=True), 11)):
+        got, st = ds.render(cp, aa=aa, **kw)
+        assert st.launches == launches and not st.wave_fallback, kw
         assert (st.rays_primary, st.rays_shadow, st.rays_reflect, st.rays_refract) == \
-            (iw["rays_primary"], iw["rays_shadow"], iw["rays_reflect"], iw["rays_refract"]), wavefront
+            (iw["rays_primary"], iw["rays_shadow"], iw["rays_reflect"], iw["rays_refract"]), kw
         frac, max8, lin = compare_images(got, want, orc.quantize)
-        assert frac >= 0.999 and max8 <= 1 and lin <= 1e-12, (wavefront, frac, max8, lin)
+        assert frac >= 0.999 and max8 <= 1 and lin <= 1e-12, (kw, frac, max8, lin)
     ds.close()
 
 
@@ -126,10 +126,10 @@ def test_overflow_and_nan_are_reported(pkg, prod, orc):
     assert e.value.code == -3                              # RTC_ERR_OVERFLOW
     c = prod.camera(16, 16, 0.5)
     c.set_transform(T.view_transform((0, 0, 0), (0, 0, 1), (0, 1, 0)))
-    for wavefront in (False, True):
+    for kw in (dict(wavefront=False), dict(wavefront=True), dict(wavefront=True, wave_levels=True)):
         with pytest.raises(pkg.RtcError) as e:
-            ds.render(c, wavefront=wavefront)
-        assert e.value.code == -3
+            ds.render(c, **kw)
+        assert e.value.code == -3, kw
     ds.close()
     # a zero direction makes the sphere's t = (-0 ± 0) / 0 = NaN: the reference panics in the sort
     # (intersection.rs:113), the oracle throws, the device reports RTC_ERR_NAN
@@ -226,7 +226,7 @@ def test_cube_epsilon_parallel_hits_survive_the_bvh_gpu(pkg, prod, orc, rotated)
     want, iw = orc.render(grazing_camera(orc.api, pkg, 48, rotated), cube_grazing_world(orc.api, pkg, rotated), threads=0)
     ds = pkg.DeviceScene(pkg.FlatScene(cube_grazing_world(prod, pkg, rotated)))
     cp = grazing_camera(prod, pkg, 48, rotated)
-    for kw in (dict(faithful=True), dict(faithful=False), dict(wavefront=True)):
+    for kw in (dict(faithful=True), dict(faithful=False), dict(wavefront=True), dict(wavefront=True, wave_levels=True)):
         got, st = ds.render(cp, **kw)
         assert st.rays == iw["rays"], kw
         assert np.max(np.abs(got - want)) <= 1e-12, kw

@@ -147,7 +147,7 @@ def test_ffi_constants_match_header():
     for name in re.findall(r"\b(RTC_(?:ERR_[A-Z]+|OK|SPHERE|PLANE|CUBE|CYLINDER|CONE|TRIANGLE|SMOOTH_TRIANGLE|GROUP|CSG|PAT_[A-Z]+|CSG_[A-Z]+))\s*=\s*(-?\d+)", text):
         m = re.search(r"pub const %s: \w+ = (-?\d+);" % name[0], rs)
         assert m and int(m.group(1)) == int(name[1]), name
-    for name, val in re.findall(r"#define\s+(RTC_(?:FLAG|OPT)_[A-Z_]+|RTC_ABI_VERSION|RTC_TRACE_STATIC_MAX)\s+(\d+)u?", text):
+    for name, val in re.findall(r"#define\s+(RTC_(?:FLAG|OPT|STAT)_[A-Z_]+|RTC_ABI_VERSION|RTC_TRACE_STATIC_MAX)\s+(\d+)u?", text):
         m = re.search(r"pub const %s: \w+ = (\d+);" % name, rs)
         assert m and int(m.group(1)) == int(val), name
 

@@ -1,7 +1,8 @@
 """N>1 path on CPU: world_size-2 `gloo` processes shard one frame exactly as the multi-GPU run does
 (cyclic row tiles, rtc_opts.rank/nranks/tile_rows), each renders ITS tiles with the host build of the
-kernel source, and the canvases are combined with the same disjoint-support reduce the NCCL gather
-variant uses. The result must be bit-identical to the unsharded frame and to the oracle."""
+kernel source, and the tiles are gathered by the very function the NCCL gather variant uses (pack → one group
+of send / recv → unpack, multigpu.gather_tiles). The result must be bit-identical to the unsharded frame and to the
+oracle; a ragged frame height (36 rows, 8-row tiles, 2 ranks) is part of the case."""
 import importlib
 import os
 import sys
@@ -32,12 +33,14 @@ def _worker(rank, world_size, port, q):
     part, info = emul.render(c, w, flat=flat, threads=2, tile_rows=tile_rows, rank=rank, nranks=world_size)
     mask = mg.owned_row_mask(H, tile_rows, rank, world_size)
     assert np.all(part[~mask] == 0.0), "a rank wrote rows it does not own"
-    t = torch.from_numpy(part.copy())
+    rows = mg.padded_rows(H, tile_rows, world_size)
+    t = torch.zeros(rows, W * 3, dtype=torch.float64)
+    t[:H] = torch.from_numpy(part.reshape(H, W * 3))
     rays = torch.tensor([info["rays"]], dtype=torch.int64)
-    dist.reduce(t, dst=0, op=dist.ReduceOp.SUM)        # disjoint supports → the sum is the gather
+    mg.gather_tiles(dist, t, rank, world_size, tile_rows)
     dist.all_reduce(rays, op=dist.ReduceOp.SUM)
     if rank == 0:
-        q.put((t.numpy(), int(rays[0])))
+        q.put((t[:H].numpy().reshape(H, W, 3).copy(), int(rays[0])))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -62,6 +65,22 @@ def test_two_rank_sharded_frame_equals_full_frame(pkg, prod, orc, emul):
     wo, co = scenes.reflect_refract(orc.api, 64, 36)
     want, iw = orc.render(co, wo, threads=0)
     assert np.array_equal(gathered, want) and rays == iw["rays"]
+
+
+def test_pack_unpack_round_trip(pkg):
+    import torch
+    mg = importlib.import_module("raytracer-challenge-rs_b200.multigpu")
+    for H, tr, n in [(1080, 8, 8), (36, 8, 2), (37, 4, 3)]:
+        rows = mg.padded_rows(H, tr, n)
+        assert rows >= H and rows % (tr * n) == 0 and rows - H < tr * n
+        src = torch.arange(rows * 6, dtype=torch.float64).view(rows, 6)
+        dst = torch.zeros_like(src)
+        for r in range(n):
+            p = mg.pack_tiles(src, r, tr, n)
+            own = [y for y in range(rows) if (y // tr) % n == r]
+            assert torch.equal(p.reshape(-1, 6), src[own])
+            mg.unpack_tiles(dst, p, r, tr, n)
+        assert torch.equal(dst, src)
 
 
 def test_tile_ownership_partitions_the_frame(pkg):
