@@ -125,7 +125,8 @@ L2_NOTE = "GPU arm: L2 flushed between timed frames (256 MB fill); CPU arm: not 
 def config_of(args, desc, cam, aa):
     """The workload, in the same keys and values for both arms (the driver compares the two dicts)."""
     return {"workload": args.workload, "desc": desc, "width": cam.hsize, "height": cam.vsize, "aa": aa, "max_depth": 5,
-            "l2": L2_NOTE, "tile_rows": args.tile_rows}
+            "l2": L2_NOTE if not getattr(args, "no_l2_flush", False) else "NOT flushed (--no-l2-flush: a profiling run, not a bench value)",
+            "tile_rows": args.tile_rows}
 
 
 def oracle_sample(orc, cam, world, aa, threads, budget_ms, H):
@@ -194,6 +195,7 @@ def main():
     ap.add_argument("--ref-rows", type=int, default=0, help="reference arm: render only this many rows (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=0.0, help="seconds of all-cores oracle work for the cpu_baseline / parity leg (default 15 at N=1, 6 at N>1)")
+    ap.add_argument("--no-l2-flush", action="store_true", help="profiling only (ncu traffic capture): no 256 MB fill ahead of the frames; such a run's numbers are not bench values")
     ap.add_argument("--no-push-tiles", action="store_true", help="N >= 3: let every rank's kernels store into rank 0's canvas themselves")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
@@ -214,6 +216,8 @@ def main():
     dist = None
     if world_size > 1:
         import torch.distributed as dist
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"    # the version banner goes to stdout, ahead of the one JSON line
         dist.init_process_group(backend="nccl", device_id=torch.device("cuda", local_rank))
     mg = importlib.import_module(PKG + ".multigpu")
     sampler = ClockSampler(local_rank) if rank == 0 else None
@@ -265,7 +269,8 @@ def main():
         sampler.mark()
     wall0 = time.perf_counter()
     for i in range(args.steps):
-        flush.fill_(float(i))            # L2 flush, outside the per-step events
+        if not args.no_l2_flush:
+            flush.fill_(float(i))        # L2 flush, outside the per-step events
         if dist is not None:
             dist.barrier()               # all ranks start the frame together
         ev[i][0].record(stream)

@@ -146,8 +146,9 @@ typedef struct rtc_opts {
                                          color_at call; aa_samples == 1 only) ...                          */
 #define RTC_OPT_RECURSIVE 8u          /* ... or the one-thread-per-pixel kernel; neither: the library picks.
                                          Both produce the same bits. */
-#define RTC_OPT_WAVE_LEVELS 16u       /* with the wavefront: 1 + 2 * max_depth level-synchronous passes (rt_wave.cuh) instead of
-                                         the one barrier-free persistent launch (rt_stream.cuh); same bits */
+#define RTC_OPT_WAVE_STREAM 16u       /* with the wavefront: ONE barrier-free persistent launch (rt_stream.cuh; experimental:
+                                         measured slower than the passes at every share of the headline frame) instead of
+                                         the 1 + 2 * max_depth level-synchronous passes (rt_wave.cuh); same bits */
 #define RTC_OPT_AVERAGE 2u            /* render_multithreaded semantics even for aa_samples == 1:
                                          Color::average = (0 + c) * (1.0/1) (camera.rs:186) */
 

@@ -28,7 +28,7 @@ HOST_LIB = os.path.join(_HERE, "host", "librth_host.so")
 RTC_OPT_FAITHFUL_TRAVERSAL = 1
 RTC_OPT_AVERAGE = 2
 RTC_OPT_WAVEFRONT = 4
-RTC_OPT_WAVE_LEVELS = 16
+RTC_OPT_WAVE_STREAM = 16
 RTC_STAT_WAVEFRONT = 1
 RTC_STAT_WAVE_FALLBACK = 2
 RTC_STAT_WAVE_OVERFLOWED = 4
@@ -181,7 +181,7 @@ def _check(rc):
 
 
 def make_opts(aa=1, max_depth=5, rows=None, tile_rows=8, rank=0, nranks=1, faithful=False, average=False, wavefront=None,
-              wave_levels=False):
+              wave_stream=False):
     o = RtcOpts()
     o.aa_samples, o.max_depth = aa, max_depth
     o.row_begin, o.row_end = (rows if rows else (0, 0))
@@ -189,8 +189,8 @@ def make_opts(aa=1, max_depth=5, rows=None, tile_rows=8, rank=0, nranks=1, faith
     o.flags = (RTC_OPT_FAITHFUL_TRAVERSAL if faithful else 0) | (RTC_OPT_AVERAGE if average else 0)
     if wavefront is not None:  # None: the library's default; True/False force one renderer (same bits either way)
         o.flags |= RTC_OPT_WAVEFRONT if wavefront else RTC_OPT_RECURSIVE
-    if wave_levels:    # the level-synchronous passes instead of the one barrier-free launch
-        o.flags |= RTC_OPT_WAVE_LEVELS
+    if wave_stream:    # one barrier-free persistent launch instead of the level-synchronous passes (experimental)
+        o.flags |= RTC_OPT_WAVE_STREAM
     return o
 
 

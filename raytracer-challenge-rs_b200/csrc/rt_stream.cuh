@@ -47,6 +47,14 @@ struct StreamArgs {
   char* ctrl;      // see the accessors below
   uint32_t epoch;  // this frame's stamp (1 … 2^31 - 1; the arena is zeroed when allocated)
   int32_t max_depth;
+  uint32_t flags;  // STREAM_* (policy switches; RTC_STREAM_FLAGS in the environment overrides the default: experiments)
+  uint32_t _pad;
+};
+enum : uint32_t {
+  STREAM_BIG_TICKETS = 1u,   // 128 slots per ticket while a queue holds plenty
+  STREAM_EAGER_PUBLISH = 2u, // when work is scarce, emission groups of >= 4 lanes publish at once instead of at the round's end
+  STREAM_JOINT_DELIVER = 4u, // the lanes of a round deliver their colours together (converged) after the round's tracing
+  STREAM_DEPTH_FIRST = 8u,   // tickets from the DEEPEST level that has a batch (pixels last) instead of the shallowest
 };
 // per level: reserved so far (front | rear << 32; front = reflection items from the queue's start, rear = refraction
 // items from its end), TOKENS of the two ends (items published and not yet handed out), heads of the two ends,
@@ -60,6 +68,9 @@ __device__ __forceinline__ unsigned long long* sc_finished(const StreamArgs& A) 
 
 __device__ __forceinline__ void st_release_u4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.release.gpu.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_u4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 __device__ __forceinline__ void red_add_u64(unsigned long long* p, unsigned long long v) {
   asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
@@ -154,6 +165,25 @@ __global__ void __launch_bounds__(128, MINB) wave_stream_kernel(SceneView S, Cam
       sl = h.y;
     }
   };
+  // Publish what the calling lanes have written (converged among `m`): ONE store-release per lane — its first item's
+  // header — is one MEMBAR.ALL.GPU for the group and orders the lane's record and rays before it; a second item's header
+  // follows as a plain strong store (program order after the release). Then the level's tokens.
+  bool scarce = false;  // work is short (this warp has been polling): children are published the moment they exist
+  auto publish = [&](unsigned m) {
+    const bool pa = pub_a != NONE, pb = pub_b != NONE;
+    const uint32_t ma = __ballot_sync(m, pa), mb = __ballot_sync(m, pb);
+    if ((ma | mb) == 0u) return;
+    if (pa | pb) {
+      WaveItem* first = A.lv[l + 1].items + (pa ? pub_a : pub_b);
+      st_release_u4(reinterpret_cast<double2*>(first) + 3, pub_ri, pa ? 0u : 1u, (A.epoch << 1) | (pa ? 0u : 1u), 0u);
+      if (pa && pb) st_relaxed_u4(reinterpret_cast<double2*>(A.lv[l + 1].items + pub_b) + 3, pub_ri, 1u, (A.epoch << 1) | 1u, 0u);
+    }
+    if ((int)lane == __ffs(m) - 1) {
+      if (ma) atomicAdd(sc_tokens(A, l + 1, 0u), (int)__popc(ma));
+      if (mb) atomicAdd(sc_tokens(A, l + 1, 1u), (int)__popc(mb));
+    }
+    pub_a = pub_b = NONE;
+  };
   // Tracer::advance<WAVE> hands a call that needs children here (divergent: only the lanes that emit in this very
   // advance() are converged). One atomicAdd per counter for the group; record and rays are written straight from
   // registers, the item headers (stamps) at the end of the round.
@@ -200,6 +230,9 @@ __global__ void __launch_bounds__(128, MINB) wave_stream_kernel(SceneView S, Cam
       w[1] = make_double2(f.refr_ray.o.z, f.refr_ray.d.x);
       w[2] = make_double2(f.refr_ray.d.y, f.refr_ray.d.z);
     }
+    // with idle warps about, a group worth a fence does not wait for the end of the round (the rest of the round is
+    // tens of µs on the frame's critical path, once per level)
+    if ((A.flags & STREAM_EAGER_PUBLISH) && scarce && __popc(m) >= 4) publish(m);
   };
   // lanes 1..D look at one level each, in parallel
   auto frame_done = [&]() -> bool {  // converged; has every item ever created been processed?
@@ -229,9 +262,15 @@ __global__ void __launch_bounds__(128, MINB) wave_stream_kernel(SceneView S, Cam
 #else
 #define RTK_ST(x)
 #endif
-  uint32_t pending = 0, t_base = 0, t_rear = 0, polls = 0;
+  uint32_t pending = 0, t_base = 0, t_rear = 0, t_left = 0, polls = 0;
   for (;;) {
     RTK_ST(const long long tc0 = clock64();)
+    if (pending == 0u && t_left > 0u) {  // the next 32 slots of a long ticket
+      t_base += 32u;
+      t_left -= 32u;
+      pending = 0xffffffffu;
+      polls = 0;
+    }
     if (pending == 0u) {
       // ---- take a ticket: pixels first, then the shallowest level with a full batch published, then (after an idle
       // poll) the shallowest level with anything published ------------------------------------------------------------
@@ -253,21 +292,32 @@ __global__ void __launch_bounds__(128, MINB) wave_stream_kernel(SceneView S, Cam
       const bool level_lane = lane >= 1u && (int)lane <= D;
       const uint32_t m_pix = __ballot_sync(0xffffffffu, lane == 0u && p0 < n0);
       const uint32_t m_full = __ballot_sync(0xffffffffu, level_lane && (tf >= 32 || tr_ >= 32));
+      const uint32_t m_plenty = __ballot_sync(0xffffffffu, level_lane && (tf >= 16384 || tr_ >= 16384));
       const uint32_t m_any = __ballot_sync(0xffffffffu, level_lane && (tf > 0 || tr_ > 0));
-      const uint32_t m_pick = m_pix ? m_pix : (m_full ? m_full : (idle > 0u ? m_any : 0u));
       uint32_t got = 0;  // slots granted
       uint32_t b_base = 0, b_rear = 0;
-      const int picker = m_pick ? __ffs(m_pick) - 1 : -1;
+      int picker;
+      if (A.flags & STREAM_DEPTH_FIRST) {
+        // deepest full batch, else a pixel ticket, else (after an idle poll) the deepest level with anything
+        const uint32_t m_pick = m_full ? m_full : (m_pix ? m_pix : (idle > 0u ? m_any : 0u));
+        picker = m_pick ? 31 - __clz(m_pick) : -1;
+      } else {
+        const uint32_t m_pick = m_pix ? m_pix : (m_full ? m_full : (idle > 0u ? m_any : 0u));
+        picker = m_pick ? __ffs(m_pick) - 1 : -1;
+      }
       if ((int)lane == picker) {
         if (lane == 0u) {
-          b_base = atomicAdd(sc_pop(A, 0, 0u), 32u);
-          got = b_base < n0 ? 32u : 0u;
+          // pixels: 128 at a time while there are plenty (the acquisition is three L2 round trips: 2.4 µs)
+          const uint32_t want = ((A.flags & STREAM_BIG_TICKETS) && p0 + 65536u <= n0) ? 128u : 32u;
+          b_base = atomicAdd(sc_pop(A, 0, 0u), want);
+          got = b_base < n0 ? min(want, n0 - b_base) : 0u;
         } else {
           b_rear = (tf >= 32 || (tr_ < 32 && tf >= tr_)) ? 0u : 1u;
           int* tok = sc_tokens(A, (int)lane, b_rear);
-          const int old = atomicAdd(tok, -32);
-          const int grant = old >= 32 ? 32 : ((old > 0 && m_full == 0u) ? old : 0);
-          if (grant < 32) atomicAdd(tok, 32 - grant);
+          const int want = ((A.flags & STREAM_BIG_TICKETS) && (b_rear ? tr_ : tf) >= 16384) ? 128 : 32;
+          const int old = atomicAdd(tok, -want);
+          const int grant = old >= want ? want : (old >= 32 ? (old & ~31) : ((old > 0 && m_full == 0u) ? old : 0));
+          if (grant < want) atomicAdd(tok, want - grant);
           RTK_ST(if (grant == 0) st_over++;)
           if (grant > 0) {
             b_base = atomicAdd(sc_pop(A, (int)lane, b_rear), (uint32_t)grant);
@@ -289,11 +339,14 @@ __global__ void __launch_bounds__(128, MINB) wave_stream_kernel(SceneView S, Cam
         }
         continue;
       }
+      // scarce: nothing but this ticket was on offer, or the warp had to wait for it
+      scarce = idle > 0u || (m_pix == 0u && m_plenty == 0u);
       idle = 0;
       l = picker;
       t_base = b_base;
       t_rear = b_rear;
       pending = got >= 32u ? 0xffffffffu : ((1u << got) - 1u);
+      t_left = got > 32u ? got - 32u : 0u;
       polls = 0;
       RTK_ST(st_batches++;)
     }
@@ -324,7 +377,8 @@ __global__ void __launch_bounds__(128, MINB) wave_stream_kernel(SceneView S, Cam
       const uint32_t k = t_base + lane;
       const uint32_t at = t_rear ? A.lv[l].cap_items - 1u - k : k;
       q = reinterpret_cast<const double2*>(A.lv[l].items + at);
-      // the stamp names the frame AND the queue end: the other end's items live in the same array, from the far side
+      // the stamp names the frame AND the queue end: the other end's items live in the same array, from the far side.
+      // (Stamp first, rays after it has been seen: four loads issued together could return a fresh stamp with stale rays.)
       if (mine) have = ld_relaxed_u32(reinterpret_cast<const uint32_t*>(q + 3) + 2) == ((A.epoch << 1) | t_rear);
     }
     const uint32_t ready = __ballot_sync(0xffffffffu, have);
@@ -355,24 +409,16 @@ __global__ void __launch_bounds__(128, MINB) wave_stream_kernel(SceneView S, Cam
         search<HAS_CSG, MODE>(S, tr.qray, tr.q, scratch.csg(), &scratch.bvh, &err);
         if (tr.template advance<true>(S, nullptr, scratch.neg, rc, &err, put)) break;
       }
-      if (!tr.w_emit) deliver(tr.result, l, parent, slot);
+      if (!(A.flags & STREAM_JOINT_DELIVER) && !tr.w_emit) deliver(tr.result, l, parent, slot);
     }
+    __syncwarp();
+    // the arrival atomics, sibling polls and record loads of a delivery are dependent L2 round trips: lane by lane as
+    // each finishes its trace they add up; together they overlap
+    if ((A.flags & STREAM_JOINT_DELIVER) && have && !tr.w_emit) deliver(tr.result, l, parent, slot);
     __syncwarp();
     // ---- publish what this round emitted: records and rays (plain stores above) before the stamps (store-release,
     // one MEMBAR per kind for the warp), then the level's published count -------------------------------------------------
-    {
-      const bool pa = pub_a != NONE, pb = pub_b != NONE;
-      const uint32_t ma = __ballot_sync(0xffffffffu, pa), mb = __ballot_sync(0xffffffffu, pb);
-      if (ma | mb) {
-        if (pa) st_release_u4(const_cast<double2*>(reinterpret_cast<const double2*>(A.lv[l + 1].items + pub_a)) + 3, pub_ri, 0u, A.epoch << 1, 0u);
-        if (pb) st_release_u4(const_cast<double2*>(reinterpret_cast<const double2*>(A.lv[l + 1].items + pub_b)) + 3, pub_ri, 1u, (A.epoch << 1) | 1u, 0u);
-        if (lane == 0u) {
-          if (ma) atomicAdd(sc_tokens(A, l + 1, 0u), (int)__popc(ma));
-          if (mb) atomicAdd(sc_tokens(A, l + 1, 1u), (int)__popc(mb));
-        }
-        pub_a = pub_b = NONE;
-      }
-    }
+    publish(0xffffffffu);
     RTK_ST(st_work += (unsigned long long)(clock64() - tc2);)
     pending &= ~ready;
     // the lanes' reservations (atomics on the reserved counts, whose results they have already used) are at L2 by now

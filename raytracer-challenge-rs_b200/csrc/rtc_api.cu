@@ -75,6 +75,8 @@ struct rtc_scene {
   bool has_branching = false;  // some material reflects AND refracts: shade_hit spawns two children, the tree grows as 2^depth
   bool last_wave = false;
   uint32_t stat_flags = 0;     // RTC_STAT_* of the frame in flight
+  cudaStream_t busy_stream = nullptr;  // stream of a frame queued by rtc_render_device and not yet finished ...
+  bool busy = false;                   // ... rtc_scene_destroy and a render on another stream wait for it
   CameraD last_cam{};
   RenderParams last_P{};
   double* last_out = nullptr;
@@ -103,6 +105,11 @@ int validate(const rtc_scene_desc* d, std::vector<int32_t>& csg_parent, bool& ha
   if (d->abi_version != RTC_ABI_VERSION) return fail(RTC_ERR_INVALID, "abi_version mismatch");
   if (d->n_nodes > 0 && !d->nodes) return fail(RTC_ERR_INVALID, "nodes is NULL");
   if (d->n_nodes > 0x7fffff00u) return fail(RTC_ERR_INVALID, "too many nodes");
+  // every non-empty table has a pointer — before any table is read (here, in build_accel, or by the upload)
+  if ((d->n_xforms && !d->xforms) || (d->n_boxes && !d->boxes) || (d->n_limits && !d->limits) ||
+      (d->n_triangles && (!d->tri_p1e1e2 || !d->tri_normals)) || (d->n_materials && !d->materials) ||
+      (d->n_patterns && !d->patterns) || (d->n_lights && !d->lights))
+    return fail(RTC_ERR_INVALID, "a non-empty table has a NULL pointer");
   const int32_t n = (int32_t)d->n_nodes;
   csg_parent.assign((size_t)n, -1);
   has_csg = false;
@@ -454,6 +461,10 @@ int launch_stream(rtc_scene* s, const CameraD& cam, const RenderParams& P, doubl
   }
   A.ctrl = base;
   A.max_depth = D;
+  {
+    static const char* env = std::getenv("RTC_STREAM_FLAGS");
+    A.flags = env ? (uint32_t)std::atoi(env) : (STREAM_JOINT_DELIVER);
+  }
   uint32_t e = g_wave_epoch.fetch_add(1) & 0x7fffffffu;
   if (e == 0) e = g_wave_epoch.fetch_add(1) & 0x7fffffffu;
   A.epoch = e;
@@ -501,6 +512,11 @@ bool use_wavefront(const rtc_scene* s, const RenderParams& P, bool faithful, uin
 }
 
 int launch_frame(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool faithful, double* out, cudaStream_t stream) {
+  // the counters, the wavefront arena and the ray-count events are per scene: a frame still in flight on ANOTHER
+  // stream must be over before they are reset (same stream: stream order does it)
+  if (s->busy && s->busy_stream != stream) CUDA_TRY(cudaStreamSynchronize(s->busy_stream));
+  s->busy = true;
+  s->busy_stream = stream;
   // counters[7] is sticky: wavefront frames whose queues overflowed since the last rtc_scene_finish
   CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, (N_COUNTERS - 1) * sizeof(unsigned long long), stream));
   CUDA_TRY(cudaEventRecord(s->ev0, stream));
@@ -509,10 +525,10 @@ int launch_frame(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool f
   int rc;
   if (s->last_wave) {
     s->last_cam = cam; s->last_P = P; s->last_out = out;
-    // one barrier-free persistent launch (rt_stream.cuh) unless the level-synchronous passes are asked for
-    static const char* env_levels = std::getenv("RTC_WAVE_LEVELS");
-    const bool levels = env_levels ? env_levels[0] == '1' : (P.flags & RTC_OPT_WAVE_LEVELS) != 0;
-    rc = levels ? launch_wave(s, cam, P, out, stream) : launch_stream(s, cam, P, out, stream);
+    // the level-synchronous passes (rt_wave.cuh), or — on request — one barrier-free persistent launch (rt_stream.cuh)
+    static const char* env_stream = std::getenv("RTC_WAVE_STREAM");
+    const bool streaming = env_stream ? env_stream[0] == '1' : (P.flags & RTC_OPT_WAVE_STREAM) != 0;
+    rc = streaming ? launch_stream(s, cam, P, out, stream) : launch_wave(s, cam, P, out, stream);
   } else {
     rc = launch_rows(s, cam, P, faithful, out, stream, 0, 0);
   }
@@ -752,6 +768,9 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
 void rtc_scene_destroy(rtc_scene* s) {
   if (!s) return;
   cudaSetDevice(s->device);
+  // a frame queued on a caller's stream may still be reading the slab, the arena and the canvas that go back to
+  // their pools below
+  if (s->busy) cudaStreamSynchronize(s->busy_stream);
   if (s->slab) {
     if (s->stream) cudaFreeAsync(s->slab, s->stream); else cudaFree(s->slab);
   }
@@ -792,7 +811,8 @@ int rtc_scene_finish(rtc_scene* s, void* stream_, rtc_stats* stats) {
   if (stats) std::memset(stats, 0, sizeof *stats);
   int rc = resolve_wave(s, stream);
   if (rc) return rc;
-  rc = read_counters(s, stream, stats);
+  rc = read_counters(s, stream, stats);  // synchronises `stream`
+  if (s->busy && s->busy_stream == stream) s->busy = false;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(RTC_ERR_CUDA, std::string("kernel: ") + cudaGetErrorString(e));
   if (stats) {

@@ -138,12 +138,13 @@ class ShardedRenderer:
                 self.recv = [torch.empty(rounds, self.tile_rows * self.row_elems, dtype=torch.float64, device="cuda:%d" % self.device)
                              for _ in range(self.nranks)]
 
-    def render_async(self, stream_ptr, aa=1, max_depth=5):
-        """Queue this rank's tiles on `stream_ptr` (a cudaStream_t as int; torch's current stream)."""
+    def render_async(self, stream_ptr, aa=1, max_depth=5, **renderer):
+        """Queue this rank's tiles on `stream_ptr` (a cudaStream_t as int; torch's current stream). `renderer`:
+        wavefront= / wave_stream= of make_opts (default: the library's choice)."""
         local = self.local
         self.scene.render_device(self.camera, local.data_ptr() if local is not None else self.canvas_ptr, stream=stream_ptr,
                                  stats=False, aa=aa, max_depth=max_depth, tile_rows=self.tile_rows, rank=self.rank,
-                                 nranks=self.nranks)
+                                 nranks=self.nranks, **renderer)
         if local is not None:
             self._push(stream_ptr)
 

@@ -44,7 +44,7 @@ pub const RTC_OPT_FAITHFUL_TRAVERSAL: u32 = 1;
 pub const RTC_OPT_AVERAGE: u32 = 2;
 pub const RTC_OPT_WAVEFRONT: u32 = 4;
 pub const RTC_OPT_RECURSIVE: u32 = 8;
-pub const RTC_OPT_WAVE_LEVELS: u32 = 16;
+pub const RTC_OPT_WAVE_STREAM: u32 = 16;
 pub const RTC_STAT_WAVEFRONT: u32 = 1;
 pub const RTC_STAT_WAVE_FALLBACK: u32 = 2;
 pub const RTC_STAT_WAVE_OVERFLOWED: u32 = 4;

@@ -17,7 +17,7 @@ n = cam.hsize * cam.vsize * 3
 canvas = torch.zeros(n, dtype=torch.float64, device="cuda")
 flush = torch.empty(64 * 1024 * 1024, dtype=torch.float32, device="cuda")
 s = torch.cuda.current_stream(); sp = s.cuda_stream
-MODES = {"recursive": dict(wavefront=False), "stream": dict(wavefront=True), "levels": dict(wavefront=True, wave_levels=True)}
+MODES = {"recursive": dict(wavefront=False), "stream": dict(wavefront=True, wave_stream=True), "levels": dict(wavefront=True)}
 def t(nr, r, mode, reps=7):
     ms = []
     for i in range(reps):

@@ -14,7 +14,7 @@ world, cam = getattr(scenes, fn)(pkg.scene_api(), **kw)
 ds = pkg.DeviceScene(pkg.FlatScene(world), device=0)
 canvas = torch.zeros(cam.hsize * cam.vsize * 3, dtype=torch.float64, device="cuda")
 s = torch.cuda.current_stream(); sp = s.cuda_stream
-for mode in (dict(wavefront=True), dict(wavefront=True, wave_levels=True)):
+for mode in (dict(wavefront=True, wave_stream=True), dict(wavefront=True)):
     for rep in range(3):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(s)

@@ -21,7 +21,7 @@ out = {"width": W, "height": H, "scene_s": time.perf_counter() - t0}
 ok = True
 ref, sr = ds.render(cam, faithful=True)
 out["faithful_kernel_ms"] = sr.kernel_ms
-for name, kw in (("recursive", dict(wavefront=False)), ("stream", dict(wavefront=True)), ("levels", dict(wavefront=True, wave_levels=True))):
+for name, kw in (("recursive", dict(wavefront=False)), ("stream", dict(wavefront=True, wave_stream=True)), ("levels", dict(wavefront=True))):
     got, st = ds.render(cam, **kw)
     same = bool(np.array_equal(got, ref))
     rays = (st.rays_primary, st.rays_shadow, st.rays_reflect, st.rays_refract) == (sr.rays_primary, sr.rays_shadow, sr.rays_reflect, sr.rays_refract)

@@ -60,3 +60,17 @@ def test_scene_validation_rejects_bad_desc(pkg, prod):
     rc = pkg.cuda_lib().rtc_scene_create(C.byref(flat.desc), 0, C.byref(h))
     nodes[0].xform = old
     assert rc == -1 and b"xform" in pkg.cuda_lib().rtc_last_error()
+
+
+def test_scene_validation_rejects_null_tables(pkg, prod):
+    """A non-empty table with a NULL pointer is RTC_ERR_INVALID before anything dereferences it (no device needed)."""
+    scenes = __import__("importlib").import_module("raytracer-challenge-rs_b200.scenes")
+    w, c = scenes.default_world(prod)
+    flat = pkg.FlatScene(w)
+    for field in ("materials", "xforms", "lights", "nodes"):
+        d = pkg.RtcSceneDesc.from_buffer_copy(flat.desc)
+        setattr(d, field, None)
+        h = C.c_void_p()
+        rc = pkg.cuda_lib().rtc_scene_create(C.byref(d), 0, C.byref(h))
+        assert rc == -1, field
+        assert b"NULL" in pkg.cuda_lib().rtc_last_error(), field

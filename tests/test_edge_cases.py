@@ -85,7 +85,7 @@ def test_big_accel_instantiations_match_oracle(case, pkg, prod, orc, monkeypatch
     monkeypatch.setenv("RTC_BIG_ACCEL", "1")
     wp, cp = scenes.CONFIGS[name](prod, **kw)
     ds = pkg.DeviceScene(pkg.FlatScene(wp))
-    for kw, launches in ((dict(wavefront=False), 1), (dict(wavefront=True), 1), (dict(wavefront=True, wave_levels=True), 11)):
+    for kw, launches in ((dict(wavefront=False), 1), (dict(wavefront=True), 11), (dict(wavefront=True, wave_stream=True), 1)):
         got, st = ds.render(cp, aa=aa, **kw)
         assert st.launches == launches and not st.wave_fallback, kw
         assert (st.rays_primary, st.rays_shadow, st.rays_reflect, st.rays_refract) == \
@@ -126,7 +126,7 @@ def test_overflow_and_nan_are_reported(pkg, prod, orc):
     assert e.value.code == -3                              # RTC_ERR_OVERFLOW
     c = prod.camera(16, 16, 0.5)
     c.set_transform(T.view_transform((0, 0, 0), (0, 0, 1), (0, 1, 0)))
-    for kw in (dict(wavefront=False), dict(wavefront=True), dict(wavefront=True, wave_levels=True)):
+    for kw in (dict(wavefront=False), dict(wavefront=True), dict(wavefront=True, wave_stream=True)):
         with pytest.raises(pkg.RtcError) as e:
             ds.render(c, **kw)
         assert e.value.code == -3, kw
@@ -226,7 +226,7 @@ def test_cube_epsilon_parallel_hits_survive_the_bvh_gpu(pkg, prod, orc, rotated)
     want, iw = orc.render(grazing_camera(orc.api, pkg, 48, rotated), cube_grazing_world(orc.api, pkg, rotated), threads=0)
     ds = pkg.DeviceScene(pkg.FlatScene(cube_grazing_world(prod, pkg, rotated)))
     cp = grazing_camera(prod, pkg, 48, rotated)
-    for kw in (dict(faithful=True), dict(faithful=False), dict(wavefront=True), dict(wavefront=True, wave_levels=True)):
+    for kw in (dict(faithful=True), dict(faithful=False), dict(wavefront=True), dict(wavefront=True, wave_stream=True)):
         got, st = ds.render(cp, **kw)
         assert st.rays == iw["rays"], kw
         assert np.max(np.abs(got - want)) <= 1e-12, kw

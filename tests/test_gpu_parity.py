@@ -63,26 +63,27 @@ def test_wavefront_is_bit_identical(case, pkg, prod):
     for depth in (5, 0, 2):
         a, sa = ds.render(cp, aa=1, max_depth=depth, wavefront=False)
         assert sa.launches == 1 and not (sa.flags & pkg.RTC_STAT_WAVEFRONT)
-        # the barrier-free persistent launch (rt_stream.cuh) and the level-synchronous passes (rt_wave.cuh)
-        for levels in (False, True):
-            b, sb = ds.render(cp, aa=1, max_depth=depth, wavefront=True, wave_levels=levels)
-            want_launches = (2 * depth + 1 if levels else 1) if depth > 0 else 1
-            assert sb.launches == want_launches and not sb.wave_fallback, (depth, levels, sb.launches)
+        # the level-synchronous passes (rt_wave.cuh) and the barrier-free persistent launch (rt_stream.cuh)
+        for stream in (False, True):
+            b, sb = ds.render(cp, aa=1, max_depth=depth, wavefront=True, wave_stream=stream)
+            want_launches = (1 if stream else 2 * depth + 1) if depth > 0 else 1
+            assert sb.launches == want_launches and not sb.wave_fallback, (depth, stream, sb.launches)
             assert bool(sb.flags & pkg.RTC_STAT_WAVEFRONT) == (depth > 0)
-            assert np.array_equal(a, b), (depth, levels)
+            assert np.array_equal(a, b), (depth, stream)
             assert (sa.rays_primary, sa.rays_shadow, sa.rays_reflect, sa.rays_refract) == \
-                (sb.rays_primary, sb.rays_shadow, sb.rays_reflect, sb.rays_refract), (depth, levels)
+                (sb.rays_primary, sb.rays_shadow, sb.rays_reflect, sb.rays_refract), (depth, stream)
     full, _ = ds.render(cp, aa=1, wavefront=False)
     parts = np.zeros_like(full)
-    for levels in (False, True):
+    for stream in (False, True):
         parts[:] = 0.0
         for r in range(3):
-            ds.render(cp, out=parts, aa=1, tile_rows=4, rank=r, nranks=3, wavefront=True, wave_levels=levels)
-        assert np.array_equal(full, parts), levels
-    # the same frame again and again through one scene handle: the queues' ready stamps are per frame
-    for _ in range(3):
-        b, _ = ds.render(cp, aa=1, wavefront=True)
-        assert np.array_equal(full, b)
+            ds.render(cp, out=parts, aa=1, tile_rows=4, rank=r, nranks=3, wavefront=True, wave_stream=stream)
+        assert np.array_equal(full, parts), stream
+    # the same frame again and again through one scene handle, the two wavefronts alternating: the streaming queues'
+    # ready stamps are per frame, and its child slots must be sentinels again after a frame of the passes
+    for k in range(4):
+        b, _ = ds.render(cp, aa=1, wavefront=True, wave_stream=(k != 2))
+        assert np.array_equal(full, b), k
     ds.close()
 
 
@@ -103,17 +104,18 @@ def test_wavefront_queue_overflow_falls_back(pkg, prod):
     ds = pkg.DeviceScene(pkg.FlatScene(w))
     a, sa = ds.render(c, wavefront=False)
     assert not sa.wave_fallback
-    for levels in (False, True):
-        b, sb = ds.render(c, wavefront=True, wave_levels=levels)
-        assert sb.wave_fallback, levels                       # the overflow path really ran ...
+    for stream in (False, True):
+        b, sb = ds.render(c, wavefront=True, wave_stream=stream)
+        assert sb.wave_fallback, stream                       # the overflow path really ran ...
         assert np.array_equal(a, b) and sa.rays == sb.rays    # ... and the frame is whole
     assert sa.rays_reflect + sa.rays_refract > 2 * 2 * 96 * 64  # some level really exceeded 2 per pixel
     # a frame that fits, right after one that did not, through the same handle
     c2 = prod.camera(96, 64, 0.9)
     c2.set_transform(pkg.transform.view_transform((0, 0, -12), (0, 0, 0), (0, 1, 0)))
     a2, _ = ds.render(c2, wavefront=False)
-    b2, sb2 = ds.render(c2, wavefront=True)
-    assert np.array_equal(a2, b2)
+    for stream in (True, False, True):
+        b2, sb2 = ds.render(c2, wavefront=True, wave_stream=stream)
+        assert np.array_equal(a2, b2) and not sb2.wave_fallback, stream
     ds.close()
 
 
