@@ -323,23 +323,35 @@ def main():
         host_ptr, host_np = shared.ptr, shared.numpy().reshape(H, W, 3)
         dist.barrier()
     e2e_fallbacks = [0]
+    phase = {"flatten": 0.0, "scene_create": 0.0, "render_call": 0.0, "render_kernels": 0.0, "scene_destroy": 0.0}
 
     def e2e_step():
+        t_a = time.perf_counter()
         f = pkg.FlatScene(world)
+        t_b = time.perf_counter()
         ds = pkg.DeviceScene(f, device=local_rank)            # H2D of the flattened scene
+        t_c = time.perf_counter()
         pkg._check(lib.rtc_render(ds.h, C.byref(cam_rtc), C.byref(opts), host_ptr, C.byref(stats)))  # render + canvas to the host
+        t_d = time.perf_counter()
         e2e_fallbacks[0] += 1 if stats.flags & pkg.RTC_STAT_WAVE_FALLBACK else 0
         ds.close()
+        t_e = time.perf_counter()
+        for k, v in (("flatten", t_b - t_a), ("scene_create", t_c - t_b), ("render_call", t_d - t_c), ("scene_destroy", t_e - t_d)):
+            phase[k] += v * 1e3
+        phase["render_kernels"] += stats.kernel_ms
         return f.info["bytes"]
     for _ in range(2):
         h2d = e2e_step()
     barrier()
     e2e_fallbacks[0] = 0
+    for k in phase:
+        phase[k] = 0.0
     t0 = time.perf_counter()
-    for _ in range(e2e_steps):
+    for k in range(e2e_steps):
         h2d = e2e_step()
-        if dist is not None:
-            dist.barrier()                                    # the frame is complete when every rank's tiles are in
+        if shared is not None:                                # the frame is complete when every rank's tiles are in:
+            shared.arrive(rank, k + 1)                        # hand-over through the shared segment (microseconds,
+            shared.wait(world_size, k + 1)                    # no collective); every rank waits for the whole frame
     torch.cuda.synchronize()
     e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
     if dist is not None:
@@ -350,9 +362,10 @@ def main():
     e2e = {"value": rays_frame / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_ms,
            "h2d_bytes_per_step": (int(h2d) + 19 * 8) * world_size, "d2h_bytes_per_step": H * W * 24,
            "d2h_bytes_per_step_rank0": owned * W * 24, "wavefront_fallbacks": e2e_fallbacks[0],
+           "rank0_ms_per_step": {k: v / e2e_steps for k, v in phase.items()},
            "definition": "every step, every rank: flatten(World) + rtc_scene_create (H2D) + rtc_render of the rank's tiles into the "
                          "host canvas (N=1: pinned; N>1: one shared pinned canvas, each rank over its own PCIe link) + rtc_scene_destroy; "
-                         "barrier per frame; max over ranks"}
+                         "frame hand-over per step through the segment (rtc_host_canvas_arrive / _wait on every rank); max over ranks"}
 
     # ---- parity of the e2e frame on rank 0 (any N), roofline, cpu baseline ------------------------------------------------
     roofline, cpu_baseline = None, None

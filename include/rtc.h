@@ -257,6 +257,12 @@ RTC_API void rtc_canvas_destroy(rtc_canvas* canvas);
 typedef struct rtc_host_canvas rtc_host_canvas;
 RTC_API int rtc_host_canvas_create(const char* name, size_t n_doubles, int device, int create, rtc_host_canvas** out);
 RTC_API double* rtc_host_canvas_ptr(rtc_host_canvas* canvas);
+/* Frame hand-over through the segment itself (the mpsc channel of camera.rs:195-207): a rank that has rendered its
+ * tiles of frame `frame` (1, 2, 3 …; rtc_render has returned, so they are in host memory) arrives; wait returns
+ * once ranks 0 … nranks-1 have all arrived at `frame` (or RTC_ERR_INVALID after timeout_s seconds). A few
+ * microseconds instead of a collective. */
+RTC_API int rtc_host_canvas_arrive(rtc_host_canvas* canvas, uint32_t rank, uint32_t frame);
+RTC_API int rtc_host_canvas_wait(rtc_host_canvas* canvas, uint32_t nranks, uint32_t frame, double timeout_s);
 RTC_API void rtc_host_canvas_destroy(rtc_host_canvas* canvas);
 
 /* Debug / known-answer entry: Vector::normalize (vector.rs:25-28) of n host vectors (xyz triples) on

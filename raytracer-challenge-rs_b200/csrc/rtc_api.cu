@@ -82,10 +82,11 @@ struct rtc_scene {
   double* last_out = nullptr;
 };
 
+constexpr size_t HOST_CANVAS_CTRL = 4096;  // arrival words of up to 64 ranks behind the pixels, one per 64-byte line
 struct rtc_host_canvas {
   std::string name;
   double* ptr = nullptr;
-  size_t bytes = 0;
+  size_t bytes = 0;        // pixels + control
   int device = 0;
   bool creator = false, registered = false;
 };
@@ -585,6 +586,28 @@ struct CanvasPool {
 };
 CanvasPool g_canvas_pool;
 
+// Streams and events of destroyed scenes, per device: creating a scene per frame (the end-to-end path of a caller
+// that hands over a fresh World every time) then costs no cudaStreamCreate / cudaEventCreate (≈ 60 µs together).
+struct StreamPool {
+  struct Item { cudaStream_t stream; cudaEvent_t ev0, ev1; };
+  std::mutex mu;
+  std::vector<Item> free_[16];
+  bool take(int dev, Item& it) {
+    std::lock_guard<std::mutex> g(mu);
+    if (dev < 0 || dev >= 16 || free_[dev].empty()) return false;
+    it = free_[dev].back();
+    free_[dev].pop_back();
+    return true;
+  }
+  bool give(int dev, const Item& it) {
+    std::lock_guard<std::mutex> g(mu);
+    if (dev < 0 || dev >= 16 || free_[dev].size() >= 8) return false;
+    free_[dev].push_back(it);
+    return true;
+  }
+};
+StreamPool g_stream_pool;
+
 // rtc_trace_rays_static: device staging for a ray batch without any allocation. One file-scope array per GPU that
 // loads the library (320 KB, held until exit): [origins 3n | directions 3n | rgb 3n | t n] at RTC_TRACE_STATIC_MAX.
 // In host code `g_trace_scratch` is only the symbol's host-side stand-in; the device address is looked up once per
@@ -695,14 +718,18 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
       pool_ready[device] = true;
     }
   }
-  if ((e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+  {
+    StreamPool::Item it;
+    if (g_stream_pool.take(device, it)) { s->stream = it.stream; s->ev0 = it.ev0; s->ev1 = it.ev1; }
+  }
+  if (!s->stream && (e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
   { int n = 0; if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && n > 0) s->sm_count = n; }
   const size_t tail = align_up(N_COUNTERS_ALLOC * sizeof(unsigned long long)) + align_up(32 * sizeof(double));
   if ((e = cudaMallocAsync((void**)&s->slab, total + tail, s->stream)) != cudaSuccess) return bail(e, "cudaMallocAsync(scene)");
   s->d_counters = (unsigned long long*)(s->slab + total);
   s->d_probe = (double*)(s->slab + total + align_up(N_COUNTERS_ALLOC * sizeof(unsigned long long)));
-  if ((e = cudaEventCreate(&s->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
-  if ((e = cudaEventCreate(&s->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
+  if (!s->ev0 && (e = cudaEventCreate(&s->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
+  if (!s->ev1 && (e = cudaEventCreate(&s->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
   const auto t_built = std::chrono::steady_clock::now();
   if (total <= ((size_t)1 << 20)) {
     // small scene: stage on the host, one H2D copy (15 separate copies would cost more than the bytes)
@@ -776,9 +803,12 @@ void rtc_scene_destroy(rtc_scene* s) {
   }
   if (s->d_canvas) g_canvas_pool.give(s->device, s->d_canvas, s->canvas_doubles);
   if (s->wave_arena) g_arena_pool.give(s->device, s->wave_arena, s->wave_bytes, s->wave_clean_px, s->wave_clean_depth);
-  if (s->ev0) cudaEventDestroy(s->ev0);
-  if (s->ev1) cudaEventDestroy(s->ev1);
-  if (s->stream) cudaStreamDestroy(s->stream);
+  // (the slab's cudaFreeAsync above is ordered on the stream; whoever takes the stream next allocates behind it)
+  if (!(s->stream && s->ev0 && s->ev1 && g_stream_pool.give(s->device, StreamPool::Item{s->stream, s->ev0, s->ev1}))) {
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->stream) cudaStreamDestroy(s->stream);
+  }
   delete s;
 }
 
@@ -916,9 +946,14 @@ int rtc_render(rtc_scene* s, const rtc_camera* camera, const rtc_opts* opts, dou
       }
     }
   }
+  static const bool timing = std::getenv("RTC_TIMING") != nullptr;
+  const auto t_queued = std::chrono::steady_clock::now();
   rtc_stats local;
   rc = rtc_scene_finish(s, s->stream, &local);
   local.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  if (timing)
+    std::fprintf(stderr, "rtc_render(staged): queue + resolve %.3f ms, kernels %.3f ms, whole call %.3f ms (rank %u of %u)\n",
+                 std::chrono::duration<double, std::milli>(t_queued - t0).count(), local.kernel_ms, local.total_ms, P.rank, P.nranks);
   if (stats) *stats = local;
   return rc;
 }
@@ -1137,7 +1172,7 @@ int rtc_host_canvas_create(const char* name, size_t n_doubles, int device, int c
   if (!out || !name || name[0] != '/' || n_doubles == 0) return fail(RTC_ERR_INVALID, "bad host canvas (name must start with '/')");
   *out = nullptr;
   CUDA_TRY(cudaSetDevice(device));
-  const size_t bytes = n_doubles * sizeof(double);
+  const size_t bytes = ((n_doubles * sizeof(double) + 4095) & ~(size_t)4095) + HOST_CANVAS_CTRL;
   int fd = shm_open(name, create ? (O_CREAT | O_RDWR) : O_RDWR, 0600);
   if (fd < 0) return fail(RTC_ERR_INVALID, std::string("shm_open(") + name + "): " + std::strerror(errno));
   if (create && ftruncate(fd, (off_t)bytes) != 0) {
@@ -1166,6 +1201,27 @@ int rtc_host_canvas_create(const char* name, size_t n_doubles, int device, int c
   return RTC_OK;
 }
 double* rtc_host_canvas_ptr(rtc_host_canvas* c) { return c ? c->ptr : nullptr; }
+static volatile uint32_t* host_canvas_word(rtc_host_canvas* c, uint32_t rank) {
+  return reinterpret_cast<volatile uint32_t*>(reinterpret_cast<char*>(c->ptr) + c->bytes - HOST_CANVAS_CTRL + 64 * (size_t)rank);
+}
+int rtc_host_canvas_arrive(rtc_host_canvas* c, uint32_t rank, uint32_t frame) {
+  if (!c || rank >= 64) return fail(RTC_ERR_INVALID, "bad host canvas arrival");
+  __atomic_store_n(host_canvas_word(c, rank), frame, __ATOMIC_RELEASE);
+  return RTC_OK;
+}
+int rtc_host_canvas_wait(rtc_host_canvas* c, uint32_t nranks, uint32_t frame, double timeout_s) {
+  if (!c || nranks == 0 || nranks > 64) return fail(RTC_ERR_INVALID, "bad host canvas wait");
+  const auto t0 = std::chrono::steady_clock::now();
+  for (uint32_t r = 0; r < nranks; r++) {
+    uint32_t spins = 0;
+    // (frames count up; a rank that is already past `frame` has arrived at it)
+    while ((int32_t)(__atomic_load_n(host_canvas_word(c, r), __ATOMIC_ACQUIRE) - frame) < 0) {
+      if ((++spins & 0x3ffu) == 0u && std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > timeout_s)
+        return fail(RTC_ERR_INVALID, "rtc_host_canvas_wait: rank " + std::to_string(r) + " did not arrive at frame " + std::to_string(frame));
+    }
+  }
+  return RTC_OK;
+}
 void rtc_host_canvas_destroy(rtc_host_canvas* c) {
   if (!c) return;
   cudaSetDevice(c->device);

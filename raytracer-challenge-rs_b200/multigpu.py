@@ -82,6 +82,14 @@ class SharedHostCanvas:
     def numpy(self):
         return np.ctypeslib.as_array((C.c_double * self.n).from_address(self.ptr))
 
+    def arrive(self, rank, frame):
+        """This rank's tiles of frame `frame` (1, 2, …) are in the canvas."""
+        self.pkg._check(self.pkg.cuda_lib().rtc_host_canvas_arrive(self.h, rank, frame))
+
+    def wait(self, nranks, frame, timeout_s=60.0):
+        """Returns once every rank has arrived at `frame`: the hand-over of the frame, through the segment itself."""
+        self.pkg._check(self.pkg.cuda_lib().rtc_host_canvas_wait(self.h, nranks, frame, timeout_s))
+
     def close(self):
         if self.h:
             self.pkg.cuda_lib().rtc_host_canvas_destroy(self.h)

@@ -196,6 +196,8 @@ extern "C" {
     pub fn rtc_canvas_destroy(canvas: *mut rtc_canvas);
     pub fn rtc_host_canvas_create(name: *const c_char, n_doubles: usize, device: c_int, create: c_int, out: *mut *mut rtc_host_canvas) -> c_int;
     pub fn rtc_host_canvas_ptr(canvas: *mut rtc_host_canvas) -> *mut f64;
+    pub fn rtc_host_canvas_arrive(canvas: *mut rtc_host_canvas, rank: u32, frame: u32) -> c_int;
+    pub fn rtc_host_canvas_wait(canvas: *mut rtc_host_canvas, nranks: u32, frame: u32, timeout_s: f64) -> c_int;
     pub fn rtc_host_canvas_destroy(canvas: *mut rtc_host_canvas);
     pub fn rtc_debug_normalize(device: c_int, n: usize, xyz_host: *const f64, out_host: *mut f64) -> c_int;
     pub fn rtc_measure_fp64(device: c_int, fused: c_int, gflops_out: *mut f64) -> c_int;

@@ -90,7 +90,8 @@ for label, world_, cam in cases:
     stats = pkg.RtcStats()
     pkg._check(pkg.cuda_lib().rtc_render(ds.h, C.byref(cam_rtc), C.byref(opts), canvas.ptr, C.byref(stats)))
     ds.close()
-    dist.barrier()
+    canvas.arrive(rank, 1)
+    canvas.wait(world, 1)
     if rank == 0:
         got = canvas.numpy().reshape(cam.vsize, cam.hsize, 3)
         same = np.array_equal(got, want)
