@@ -15,6 +15,17 @@ namespace rtk {
 struct AccelStats { unsigned long long walks, bvh_nodes, prim_tests, chain_calls, chain_boxes, always_tests, sph_culled; };
 inline AccelStats& accel_stats() { static AccelStats s; return s; }
 #define RTK_COUNT(f, n) (accel_stats().f += (n))
+#elif defined(RTK_DEVICE_STATS) && defined(__CUDACC__)
+// -DRTK_DEVICE_STATS (experiments: the algorithmic byte count of a frame): the same counters on the device, one set per
+// SM to keep the atomics apart; rtc_scene_finish prints the sums. Exact, slow.
+enum { DST_walks, DST_bvh_nodes, DST_prim_tests, DST_chain_calls, DST_chain_boxes, DST_always_tests, DST_sph_culled, DST_N };
+__device__ unsigned long long g_dev_stats[256][8];
+__device__ __forceinline__ unsigned dev_smid() { unsigned r; asm volatile("mov.u32 %0, %%smid;" : "=r"(r)); return r & 255u; }
+#if defined(__CUDA_ARCH__)
+#define RTK_COUNT(f, n) atomicAdd(&g_dev_stats[dev_smid()][DST_##f], (unsigned long long)(n))
+#else
+#define RTK_COUNT(f, n) ((void)0)
+#endif
 #else
 #define RTK_COUNT(f, n) ((void)0)
 #endif

@@ -95,6 +95,12 @@ struct AccelBuild {
   SphCull sph_cull[SPH_CULL_MAX];
   CubeDir cube_dirs[CUBE_DIR_MAX] = {};
   int32_t n_cube_dirs = 0;
+  // device build (rt_accel_device.cuh): the host did the walk (every-ray prims, group parents) and left the tree to
+  // the GPU — `cand` are the BVH prims' node indices, `fwd` the forward matrices (12 per transform, NaN when singular)
+  bool deferred = false;
+  bool cand_generic = false;  // some BVH prim is not a triangle or a sphere
+  std::vector<int32_t> cand;
+  std::vector<double> fwd;
 };
 
 namespace accel_detail {
@@ -614,11 +620,29 @@ inline void mark_cube_subtrees(AccelBuild& A) {
   }
 }
 
-// `d` must already be structurally valid (rtc_api.cu validate()).
-inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
+// `d` must already be structurally valid (rtc_api.cu validate()). device_min > 0: with at least that many BVH-eligible
+// leaves (and no cube among them) only the walk is done here and the tree is left to the GPU (A.deferred).
+inline void build_accel(const rtc_scene_desc* d, AccelBuild& A, size_t device_min = 0) {
   using namespace accel_detail;
   const auto t0 = std::chrono::steady_clock::now();
   const int32_t n = (int32_t)d->n_nodes;
+  A.deferred = false;
+  A.cand_generic = false;
+  A.cand.clear();
+  A.fwd.clear();
+  bool defer = false;
+  if (device_min > 0) {
+    size_t eligible = 0;
+    bool any_cube = false;
+    for (int32_t i = 0; i < n;) {
+      const rtc_node& nd = d->nodes[i];
+      if (nd.kind == RTC_CSG) { i = nd.skip; continue; }
+      if (nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE || nd.kind == RTC_SPHERE || nd.kind == RTC_CYLINDER) eligible++;
+      if (nd.kind == RTC_CUBE) any_cube = true;
+      i++;
+    }
+    defer = eligible >= device_min && !any_cube;
+  }
   A.parent.assign((size_t)n, -1);
   A.prims.clear();
   A.n_always = 0;
@@ -643,7 +667,21 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
     } else {
       Prim p;
       p.node = i;
-      if (nd.kind != RTC_PLANE && leaf_world_box(d, nd, p.box, fwd_cache, cubes_ok)) {
+      if (defer) {
+        // eligibility without the box (the GPU computes it; a non-finite one sends the whole build back here)
+        bool ok = (nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE || nd.kind == RTC_SPHERE || nd.kind == RTC_CYLINDER) &&
+                  fwd_cache.get(d, nd.xform) != nullptr;
+        if (ok && nd.kind == RTC_CYLINDER) {
+          const double y0 = d->limits[2 * (size_t)nd.aux], y1 = d->limits[2 * (size_t)nd.aux + 1];
+          ok = std::isfinite(y0) && std::isfinite(y1) && y0 <= y1;
+        }
+        if (ok) {
+          A.cand.push_back(i);
+          if (nd.kind == RTC_CYLINDER) A.cand_generic = true;
+        } else {
+          A.prims.push_back(i);
+        }
+      } else if (nd.kind != RTC_PLANE && leaf_world_box(d, nd, p.box, fwd_cache, cubes_ok)) {
         for (int a = 0; a < 3; a++) p.c[a] = 0.5 * (p.box.lo[a] + p.box.hi[a]);
         cand.push_back(p);
       } else {
@@ -675,6 +713,20 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A) {
       while (a >= 0 && contains(a, g)) a = real_parent[(size_t)a];
       A.parent[(size_t)g] = a;
     }
+  }
+  if (defer) {
+    A.n_always = (int32_t)A.prims.size();
+    A.n_cube_dirs = 0;
+    fill_recs(d, A);
+    A.deferred = true;
+    A.fwd.assign(12 * (size_t)d->n_xforms, std::numeric_limits<double>::quiet_NaN());
+    for (uint32_t x = 0; x < d->n_xforms; x++)
+      if (fwd_cache.state[x] > 0)
+        for (int c = 0; c < 12; c++) A.fwd[12 * (size_t)x + c] = fwd_cache.m[12 * (size_t)x + c];
+    if (std::getenv("RTC_TIMING"))
+      std::fprintf(stderr, "build_accel: walk + parents %.1f ms, %zu BVH prims left to the GPU\n",
+                   std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(), A.cand.size());
+    return;
   }
   if ((int)cand.size() < BVH_MIN_PRIMS) {
     for (auto& p : cand) A.prims.push_back(p.node);

@@ -19,6 +19,7 @@
 #include <sys/stat.h>
 #include <unistd.h>
 
+#include "rt_accel_device.cuh"
 #include "rt_stream.cuh"
 
 using namespace rtk;
@@ -26,6 +27,7 @@ using namespace rtk;
 namespace {
 
 thread_local std::string g_err;
+thread_local bool g_host_build_only = false;  // rtc_scene_create retrying after the device builder declined
 
 int fail(int code, const std::string& msg) {
   g_err = msg;
@@ -167,6 +169,22 @@ int read_counters(rtc_scene* s, cudaStream_t stream, rtc_stats* stats) {
   unsigned long long h[N_COUNTERS];
   CUDA_TRY(cudaMemcpyAsync(h, s->d_counters, sizeof h, cudaMemcpyDeviceToHost, stream));
   CUDA_TRY(cudaStreamSynchronize(stream));
+#if defined(RTK_DEVICE_STATS)
+  {
+    static unsigned long long host[256][8];
+    unsigned long long* dev = nullptr;
+    if (cudaGetSymbolAddress((void**)&dev, g_dev_stats) == cudaSuccess && cudaMemcpy(host, dev, sizeof host, cudaMemcpyDeviceToHost) == cudaSuccess) {
+      unsigned long long sum[8] = {0};
+      for (int m = 0; m < 256; m++) for (int k = 0; k < 8; k++) sum[k] += host[m][k];
+      cudaMemset(dev, 0, sizeof host);
+      const unsigned long long rays = h[0] + h[1] + h[2] + h[3];
+      // every-ray prims: one 128-byte PrimRec each; BVH: 128-byte nodes, 96-byte leaf records (prim_tests counts both kinds of prim)
+      std::fprintf(stderr, "device stats: rays %llu searches %llu bvh nodes %llu prim tests %llu chain calls %llu chain boxes %llu | per ray: %.2f nodes, %.2f prims\n",
+                   rays, sum[DST_walks], sum[DST_bvh_nodes], sum[DST_prim_tests], sum[DST_chain_calls], sum[DST_chain_boxes],
+                   rays ? (double)sum[DST_bvh_nodes] / rays : 0.0, rays ? (double)sum[DST_prim_tests] / rays : 0.0);
+    }
+  }
+#endif
 #if defined(RTK_STREAM_STATS)
   if (s->stat_flags & RTC_STAT_WAVEFRONT) {
     unsigned long long d[16];
@@ -659,7 +677,18 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   CUDA_TRY(cudaSetDevice(device));
 
   AccelBuild accel;
-  build_accel(d, accel);
+  {
+    // RTC_DEVICE_BVH_MIN = n: from n BVH prims on, the host only walks the nodes and the tree is built on the GPU
+    // (rt_accel_device.cuh). Off by default: built in milliseconds instead of 0.4 s for a million triangles, but its
+    // Morton-contiguous nodes overlap more than the host's SAH tree — twice the node visits per ray on both mesh scenes
+    // (profiles/r02r_leaf_stats.log), so a scene that is rendered more than a few times is better off with the host tree.
+    const char* env = std::getenv("RTC_DEVICE_BVH_MIN");
+    const size_t device_min = env ? (size_t)std::atoll(env) : (size_t)0;
+    build_accel(d, accel, g_host_build_only ? 0 : device_min);
+  }
+  const size_t n_dev = accel.deferred ? accel.cand.size() : 0;
+  const size_t n_bvh_nodes = accel.deferred ? devbuild::node_count((int)n_dev) : accel.bvh.size();
+  const size_t n_leaf_recs = accel.deferred ? n_dev : accel.leaf_recs.size();
   const auto t_accel = std::chrono::steady_clock::now();
   // one slab: [nodes | xforms | boxes | limits | tri_geom | tri_normals | materials | patterns | lights | csg_parent
   //            | parent | prims | bvh | recs | leaf_recs]
@@ -677,12 +706,13 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
       {csg_parent.data(), sizeof(int32_t) * csg_parent.size(), 0},
       {accel.parent.data(), sizeof(int32_t) * accel.parent.size(), 0},
       {accel.prims.data(), sizeof(int32_t) * accel.prims.size(), 0},
-      {accel.bvh.data(), sizeof(BvhNode) * accel.bvh.size(), 0},
+      {accel.deferred ? nullptr : accel.bvh.data(), sizeof(BvhNode) * n_bvh_nodes, 0},
       {accel.recs.data(), sizeof(PrimRec) * accel.recs.size(), 0},
-      {accel.leaf_recs.data(), sizeof(LeafRec) * accel.leaf_recs.size(), 0}};
+      {accel.deferred ? nullptr : accel.leaf_recs.data(), sizeof(LeafRec) * n_leaf_recs, 0}};
   size_t total = 0;
-  for (auto& p : parts) {
-    if (p.bytes && !p.src) return fail(RTC_ERR_INVALID, "a non-empty table has a NULL pointer");
+  for (int k = 0; k < 15; k++) {
+    Part& p = parts[k];
+    if (p.bytes && !p.src && !(accel.deferred && (k == 12 || k == 14))) return fail(RTC_ERR_INVALID, "a non-empty table has a NULL pointer");
     p.off = total;
     total += align_up(p.bytes);
   }
@@ -693,7 +723,7 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   for (uint32_t m = 0; m < d->n_materials; m++)
     if (d->materials[m].reflective != 0.0 && d->materials[m].transparency != 0.0) s->has_branching = true;
   // 126 MB of L2 on B200: past ~64 MB of nodes + leaf records, traversal is DRAM-latency bound
-  s->big_accel = sizeof(BvhNode) * accel.bvh.size() + sizeof(LeafRec) * accel.leaf_recs.size() > ((size_t)64 << 20);
+  s->big_accel = sizeof(BvhNode) * n_bvh_nodes + sizeof(LeafRec) * n_leaf_recs > ((size_t)64 << 20);
   if (const char* env = std::getenv("RTC_BIG_ACCEL")) s->big_accel = env[0] == '1';  // experiments: force the 32-warp kernels on/off
   s->slab_bytes = total;
   auto bail = [&](cudaError_t e, const char* what) {
@@ -735,15 +765,49 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
     // small scene: stage on the host, one H2D copy (15 separate copies would cost more than the bytes)
     std::vector<char> stage(total, 0);
     for (auto& p : parts)
-      if (p.bytes) std::memcpy(stage.data() + p.off, p.src, p.bytes);
+      if (p.bytes && p.src) std::memcpy(stage.data() + p.off, p.src, p.bytes);
     if ((e = cudaMemcpyAsync(s->slab, stage.data(), total, cudaMemcpyHostToDevice, s->stream)) != cudaSuccess) return bail(e, "cudaMemcpy(scene)");
     if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return bail(e, "cudaStreamSynchronize");
   } else {
     // large scene (meshes): each table straight from where it lies, no host-side gather of hundreds of MB
     for (auto& p : parts)
-      if (p.bytes && (e = cudaMemcpyAsync(s->slab + p.off, p.src, p.bytes, cudaMemcpyHostToDevice, s->stream)) != cudaSuccess)
+      if (p.bytes && p.src && (e = cudaMemcpyAsync(s->slab + p.off, p.src, p.bytes, cudaMemcpyHostToDevice, s->stream)) != cudaSuccess)
         return bail(e, "cudaMemcpy(scene table)");
     if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return bail(e, "cudaStreamSynchronize");
+  }
+  const auto t_uploaded = std::chrono::steady_clock::now();
+  if (accel.deferred) {
+    // the tree and the leaf records, on the GPU, from the tables that have just arrived
+    char* tmp = nullptr;
+    const size_t cand_bytes = align_up(sizeof(int32_t) * n_dev), fwd_bytes = align_up(sizeof(double) * accel.fwd.size());
+    if ((e = cudaMallocAsync((void**)&tmp, cand_bytes + fwd_bytes, s->stream)) != cudaSuccess) return bail(e, "cudaMallocAsync(device build)");
+    devbuild::In in;
+    in.nodes = (const rtc_node*)(s->slab + parts[0].off);
+    in.limits = (const double*)(s->slab + parts[3].off);
+    in.tri_geom = (const double*)(s->slab + parts[4].off);
+    in.parent = (const int32_t*)(s->slab + parts[10].off);
+    in.cand = (const int32_t*)tmp;
+    in.fwd = (const double*)(tmp + cand_bytes);
+    in.n = (int32_t)n_dev;
+    bool ok = false;
+    int depth = 0;
+    e = cudaMemcpyAsync(tmp, accel.cand.data(), sizeof(int32_t) * n_dev, cudaMemcpyHostToDevice, s->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(tmp + cand_bytes, accel.fwd.data(), sizeof(double) * accel.fwd.size(), cudaMemcpyHostToDevice, s->stream);
+    if (e == cudaSuccess)
+      e = devbuild::build(in, accel.n_always, (BvhNode*)(s->slab + parts[12].off), (LeafRec*)(s->slab + parts[14].off), s->stream, &ok, &depth);
+    cudaFreeAsync(tmp, s->stream);
+    if (e != cudaSuccess) return bail(e, "device BVH build");
+    if (std::getenv("RTC_TIMING"))
+      std::fprintf(stderr, "device BVH build: %zu prims, %zu nodes, depth %d, %.2f ms%s\n", n_dev, n_bvh_nodes, depth,
+                   std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_uploaded).count(),
+                   ok ? "" : " — declined (non-finite box or tree too deep): host builder");
+    if (!ok) {
+      rtc_scene_destroy(s);
+      g_host_build_only = true;
+      const int rc2 = rtc_scene_create(d, device, out);
+      g_host_build_only = false;
+      return rc2;
+    }
   }
   if (std::getenv("RTC_TIMING")) {
     auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
@@ -775,12 +839,12 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   for (int k = 0; k < SPH_CULL_MAX; k++) v.sph_cull[k] = accel.sph_cull[k];
   for (int k = 0; k < CUBE_DIR_MAX; k++) v.cube_dirs[k] = accel.cube_dirs[k];
   v.n_cube_dirs = accel.n_cube_dirs;
-  v.n_bvh = (int32_t)accel.bvh.size();
+  v.n_bvh = (int32_t)n_bvh_nodes;
   v.n_nodes = (int32_t)d->n_nodes;
   v.n_lights = (int32_t)d->n_lights;
   v.has_csg = has_csg ? 1 : 0;
-  s->lean = !has_csg && accel.bvh.empty() && accel.n_always == accel.n_sph + accel.n_pl;
-  s->tri_sph_only = !has_csg && !accel.bvh.empty() && accel.n_always == accel.n_sph + accel.n_pl;
+  s->lean = !has_csg && n_bvh_nodes == 0 && accel.n_always == accel.n_sph + accel.n_pl;
+  s->tri_sph_only = !has_csg && n_bvh_nodes != 0 && accel.n_always == accel.n_sph + accel.n_pl && !(accel.deferred && accel.cand_generic);
   for (const LeafRec& lr : accel.leaf_recs) {
     const uint32_t k = lr.kind_flags >> 24;
     if (k != RTC_SPHERE && k != RTC_TRIANGLE && k != RTC_SMOOTH_TRIANGLE) { s->tri_sph_only = false; break; }

@@ -231,3 +231,24 @@ def test_cube_epsilon_parallel_hits_survive_the_bvh_gpu(pkg, prod, orc, rotated)
         assert st.rays == iw["rays"], kw
         assert np.max(np.abs(got - want)) <= 1e-12, kw
     ds.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", [MESH_CASES[0], MESH_CASES[1], ("solids_field", dict(width=96, height=54), 1)], ids=case_id)
+def test_device_built_bvh_matches_oracle(case, pkg, prod, orc, monkeypatch):
+    """RTC_DEVICE_BVH_MIN: the acceleration structure built on the GPU (rt_accel_device.cuh: Morton sort, SAH cuts over the
+    Morton order, one warp per node) instead of the host's SAH builder. The search result never depends on the tree, so
+    the frame must be the oracle's bit for bit — recursive kernel, both wavefronts, and the faithful traversal beside it.
+    (solids_field has cubes in the tree: the device builder must step aside for the host's.)"""
+    name, kw, aa = case
+    wo, co = scenes.CONFIGS[name](orc.api, **kw)
+    want, iw = orc.render(co, wo, aa=aa, threads=0)
+    monkeypatch.setenv("RTC_DEVICE_BVH_MIN", "16")
+    wp, cp = scenes.CONFIGS[name](prod, **kw)
+    ds = pkg.DeviceScene(pkg.FlatScene(wp))
+    for kwr in (dict(wavefront=False), dict(faithful=True), dict(wavefront=True), dict(wavefront=True, wave_stream=True)):
+        got, st = ds.render(cp, aa=aa, **kwr)
+        assert st.rays == iw["rays"], kwr
+        frac, max8, lin = compare_images(got, want, orc.quantize)
+        assert frac >= 0.999 and max8 <= 1 and lin <= 1e-12, (kwr, frac, max8, lin)
+    ds.close()
