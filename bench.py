@@ -395,13 +395,18 @@ def main():
             cpu_baseline["parity_max_linear_diff"] = float(np.max(np.abs(got - want)))
             cpu_baseline["rays_match"] = bool(rows < H or info["rays"] == rays_frame)
             if world_size == 1:
-                # Camera::render (camera.rs:133), one thread, on a few rows of the same block
+                # Camera::render (camera.rs:133), one thread: a few rows spread over the same block (about 4 s of work)
                 srows = min(rows, max(4, int(rows * 4000.0 / max(info["ms"] * cores, 1.0))))
-                s0 = (H - srows) // 2
-                _, sinfo = orc.render(co, wo, aa=aa, threads=0 if aa == 1 else 1, rows=(s0, s0 + srows))
-                cpu_baseline["serial"] = {"value": sinfo["rays"] / (sinfo["ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "cores": 1,
-                                          "frame_ms_extrapolated": sinfo["ms"] * H / srows,
-                                          "sample": "rows [%d,%d) of %d, Camera::render, 1 thread" % (s0, s0 + srows, H)}
+                step_r = max(1, rows // srows)
+                picks = list(range(r0 + step_r // 2, r0 + rows, step_r))[:srows]
+                s_ms, s_rays = 0.0, 0
+                for y in picks:
+                    _, sinfo = orc.render(co, wo, aa=aa, threads=0 if aa == 1 else 1, rows=(y, y + 1))
+                    s_ms += sinfo["ms"]
+                    s_rays += sinfo["rays"]
+                cpu_baseline["serial"] = {"value": s_rays / (s_ms * 1e-3) / 1e6, "unit": "Mrays/s", "cores": 1,
+                                          "frame_ms_extrapolated": s_ms * H / len(picks),
+                                          "sample": "%d rows spread over [%d,%d) of %d, Camera::render, 1 thread" % (len(picks), r0, r0 + rows, H)}
         # dram bytes per launch of the render kernel from the committed ncu --set full capture, if any
         traffic = None
         try:

@@ -160,8 +160,22 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
     int32_t lr_xf = -1;
     V3 inv = v3(0.0, 0.0, 0.0);
     bool have_inv = false, plain = false;
-    bool cube_near = false;  // the ray is EPSILON-parallel to a face family of a cube in the BVH (CubeDir)
     int sp = 0;
+    // -DRTK_SHARED_STACK=n (A/B of the "per-warp shared-memory stack" of the brief): the first n entries of the traversal
+    // stack live in shared memory ([entry][thread]: conflict-free), the rest in the thread's local BvhStack.
+#if defined(RTK_SHARED_STACK) && defined(__CUDA_ARCH__)
+    constexpr int SH_N = RTK_SHARED_STACK;
+    __shared__ int32_t sh_node[SH_N][128];
+    __shared__ double sh_tmin[SH_N][128];
+    const int sh_t = threadIdx.x & 127;
+#define RTK_ST_NODE(k) ((k) < SH_N ? sh_node[(k)][sh_t] : st->node[(k) - SH_N])
+#define RTK_ST_TMIN(k) ((k) < SH_N ? sh_tmin[(k)][sh_t] : st->tmin[(k) - SH_N])
+#define RTK_ST_PUSH(k, n, t) do { if ((k) < SH_N) { sh_node[(k)][sh_t] = (n); sh_tmin[(k)][sh_t] = (t); } else { st->node[(k) - SH_N] = (n); st->tmin[(k) - SH_N] = (t); } } while (0)
+#else
+#define RTK_ST_NODE(k) (st->node[(k)])
+#define RTK_ST_TMIN(k) (st->tmin[(k)])
+#define RTK_ST_PUSH(k, n, t) do { st->node[(k)] = (n); st->tmin[(k)] = (t); } while (0)
+#endif
     // one candidate intersection: want → validate against the reference's group chain → take
     auto cand = [&](double t, int32_t i, uint32_t flags, int32_t par) {
       const bool nan = t != t;
@@ -366,19 +380,31 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
         plain = ray.d.x != 0.0 && ray.d.y != 0.0 && ray.d.z != 0.0 && ray.d.x == ray.d.x && ray.d.y == ray.d.y && ray.d.z == ray.d.z;
         have_inv = true;
         if constexpr (!NO_GENERIC) {
+          // a ray EPSILON-parallel to a face family of a cube in the BVH (CubeDir): no box bounds that cube's hits for
+          // it, so it gets NO culling at all — a zero reciprocal direction makes every slab interval [0, 0]: every box
+          // test passes and no t-range rejects (the walk visits the whole tree; such rays are a 1e-5 sliver of
+          // directions, and scenes with more than 65 536 BVH prims keep their cubes out of the tree)
+          bool cube_near = false;
+          if (S.n_cube_dirs > 0) {
           const double slack = 1e-24 * dot(ray.d, ray.d);
-          for (int k = 0; k < S.n_cube_dirs; k++) {
+          // (unrolled over the parameter-bank table: a loop index would make the compiler address SceneView dynamically)
+#if defined(__CUDACC__)
+#pragma unroll
+#endif
+          for (int k = 0; k < CUBE_DIR_MAX; k++) {
             const CubeDir& cd = S.cube_dirs[k];
             const double x = cd.ux * ray.d.x + cd.uy * ray.d.y + cd.uz * ray.d.z;
-            cube_near = cube_near || x * x < cd.th2 + slack;
+            cube_near = cube_near || (k < S.n_cube_dirs && x * x < cd.th2 + slack);
           }
+          }
+          if (cube_near) { inv = v3(0.0, 0.0, 0.0); plain = false; }
         }
         cur = 0;
       } else {
         cur = NONE;
         while (sp > 0) {
           sp--;
-          if (!C.cull(st->tmin[sp], rt_inf())) { cur = st->node[sp]; break; }
+          if (!C.cull(RTK_ST_TMIN(sp), rt_inf())) { cur = RTK_ST_NODE(sp); break; }
         }
         if (cur == NONE) return;
       }
@@ -391,24 +417,17 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
         const double2* bq = reinterpret_cast<const double2*>(bn);
         const double2 q0 = __ldg(bq), q1 = __ldg(bq + 1), q2 = __ldg(bq + 2), q3 = __ldg(bq + 3), q4 = __ldg(bq + 4), q5 = __ldg(bq + 5);
         const int4 ci = __ldg(reinterpret_cast<const int4*>(&bn->c0));
-        const int32_t c0r = ci.x, n0 = ci.y, c1r = ci.z, n1 = ci.w;
+        const int32_t c0 = ci.x, n0 = ci.y, c1 = ci.z, n1 = ci.w;
         const double l0x = q0.x, l0y = q0.y, l0z = q1.x, h0x = q1.y, h0y = q2.x, h0z = q2.y;
         const double l1x = q3.x, l1y = q3.y, l1z = q4.x, h1x = q4.y, h1y = q5.x, h1z = q5.y;
 #else
-        const int32_t c0r = bn->c0, n0 = bn->n0, c1r = bn->c1, n1 = bn->n1;
+        const int32_t c0 = bn->c0, n0 = bn->n0, c1 = bn->c1, n1 = bn->n1;
         const double l0x = bn->lo0[0], l0y = bn->lo0[1], l0z = bn->lo0[2], h0x = bn->hi0[0], h0y = bn->hi0[1], h0z = bn->hi0[2];
         const double l1x = bn->lo1[0], l1y = bn->lo1[1], l1z = bn->lo1[2], h1x = bn->hi1[0], h1y = bn->hi1[1], h1z = bn->hi1[2];
 #endif
         double t0min = 0.0, t0max = 0.0, t1min = 0.0, t1max = 0.0;
-        const int32_t c0 = c0r & ~BVH_CUBE_BIT, c1 = c1r & ~BVH_CUBE_BIT;
-        bool h0 = n0 >= 0 && own_box(l0x, l0y, l0z, h0x, h0y, h0z, ray, inv, plain, t0min, t0max) && !C.cull(t0min, t0max);
-        bool h1 = n1 >= 0 && own_box(l1x, l1y, l1z, h1x, h1y, h1z, ray, inv, plain, t1min, t1max) && !C.cull(t1min, t1max);
-        if constexpr (!NO_GENERIC) {
-          if (cube_near) {  // no box bounds a cube's hits for this ray: every subtree holding a cube is visited
-            if (!h0 && n0 >= 0 && (c0r & BVH_CUBE_BIT)) { h0 = true; t0min = -rt_inf(); }
-            if (!h1 && n1 >= 0 && (c1r & BVH_CUBE_BIT)) { h1 = true; t1min = -rt_inf(); }
-          }
-        }
+        const bool h0 = n0 >= 0 && own_box(l0x, l0y, l0z, h0x, h0y, h0z, ray, inv, plain, t0min, t0max) && !C.cull(t0min, t0max);
+        const bool h1 = n1 >= 0 && own_box(l1x, l1y, l1z, h1x, h1y, h1z, ray, inv, plain, t1min, t1max) && !C.cull(t1min, t1max);
         // refs: >= 0 inner node, < 0 leaf ~(first << 3 | count)
         const int32_t r0 = n0 > 0 ? ~((c0 << 3) | n0) : c0;
         const int32_t r1 = n1 > 0 ? ~((c1 << 3) | n1) : c1;
@@ -416,8 +435,7 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
         if (h0 && h1) {
           const bool swap = t1min < t0min;  // near child first, far child on the stack with its tmin
           if (sp < BVH_STACK) {
-            st->node[sp] = swap ? r0 : r1;
-            st->tmin[sp] = swap ? t0min : t1min;
+            RTK_ST_PUSH(sp, swap ? r0 : r1, swap ? t0min : t1min);
             sp++;
           } else {
             *err |= ERR_OVERFLOW;
@@ -428,7 +446,7 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
         } else {
           while (sp > 0) {
             sp--;
-            if (!C.cull(st->tmin[sp], rt_inf())) { cur = st->node[sp]; break; }
+            if (!C.cull(RTK_ST_TMIN(sp), rt_inf())) { cur = RTK_ST_NODE(sp); break; }
           }
         }
       }

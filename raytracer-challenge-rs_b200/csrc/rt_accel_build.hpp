@@ -74,10 +74,11 @@ struct SphCull {
 // lies outside the cube by up to EPSILON * t. No box bounds those, so a ray that is near-parallel to a face family of
 // some cube in the BVH must not be culled away from cubes. The face families (unit normals u, and the largest
 // theta = EPSILON / |row| of the cubes sharing u: |row . d| < EPSILON  <=>  |u . d| < theta) travel in SceneView; a ray
-// with (u . d)^2 < th2 + 1e-24 d.d for some family descends into every BVH child whose subtree holds a cube
-// (BVH_CUBE_BIT of c0 / c1) regardless of the box test. More than CUBE_DIR_MAX families: cubes stay every-ray prims.
+// with (u . d)^2 < th2 + 1e-24 d.d for some family walks the tree without any culling (rt_accel.cuh). More than
+// CUBE_DIR_MAX families, or more than CUBE_BVH_MAX_PRIMS prims in the tree (an unculled walk of a big mesh is a cliff):
+// cubes stay every-ray prims.
 constexpr int CUBE_DIR_MAX = 6;
-constexpr int32_t BVH_CUBE_BIT = 1 << 30;
+constexpr size_t CUBE_BVH_MAX_PRIMS = 65536;
 struct CubeDir {
   double ux, uy, uz;
   double th2;  // 2 * theta^2 * (1 + 1e-6): (a + b)^2 <= 2 a^2 + 2 b^2 covers the clustering tolerance of u
@@ -588,38 +589,6 @@ inline bool cube_face_families(const rtc_scene_desc* d, AccelBuild& A) {
   return true;
 }
 
-// BVH_CUBE_BIT on every child reference whose subtree holds a cube (after Builder::build; leaf ranges are already
-// shifted by the always-prefix).
-inline void mark_cube_subtrees(AccelBuild& A) {
-  if (A.bvh.empty() || A.n_cube_dirs == 0) return;
-  std::vector<signed char> memo(A.bvh.size(), -1);
-  auto leaf_has = [&](int32_t c, int32_t n) {
-    for (int32_t k = c; k < c + n; k++)
-      if ((A.leaf_recs[(size_t)(k - A.n_always)].kind_flags >> 24) == (uint32_t)RTC_CUBE) return true;
-    return false;
-  };
-  // iterative post-order (depth is bounded, but a million-node tree should not recurse on the host stack)
-  std::vector<int32_t> stack{0};
-  while (!stack.empty()) {
-    const int32_t i = stack.back();
-    BvhNode& nd = A.bvh[(size_t)i];
-    bool ready = true;
-    if (nd.n0 == 0 && memo[(size_t)nd.c0] < 0) { stack.push_back(nd.c0); ready = false; }
-    if (nd.n1 == 0 && memo[(size_t)nd.c1] < 0) { stack.push_back(nd.c1); ready = false; }
-    if (!ready) continue;
-    stack.pop_back();
-    const bool h0 = nd.n0 > 0 ? leaf_has(nd.c0, nd.n0) : (nd.n0 == 0 ? memo[(size_t)nd.c0] > 0 : false);
-    const bool h1 = nd.n1 > 0 ? leaf_has(nd.c1, nd.n1) : (nd.n1 == 0 ? memo[(size_t)nd.c1] > 0 : false);
-    memo[(size_t)i] = (h0 || h1) ? 1 : 0;
-  }
-  for (BvhNode& nd : A.bvh) {
-    const bool h0 = nd.n0 > 0 ? leaf_has(nd.c0, nd.n0) : (nd.n0 == 0 ? memo[(size_t)nd.c0] > 0 : false);
-    const bool h1 = nd.n1 > 0 ? leaf_has(nd.c1, nd.n1) : (nd.n1 == 0 ? memo[(size_t)nd.c1] > 0 : false);
-    if (h0) nd.c0 |= BVH_CUBE_BIT;
-    if (h1) nd.c1 |= BVH_CUBE_BIT;
-  }
-}
-
 // `d` must already be structurally valid (rtc_api.cu validate()). device_min > 0: with at least that many BVH-eligible
 // leaves (and no cube among them) only the walk is done here and the tree is left to the GPU (A.deferred).
 inline void build_accel(const rtc_scene_desc* d, AccelBuild& A, size_t device_min = 0) {
@@ -650,7 +619,18 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A, size_t device_mi
   A.leaf_recs.clear();
   std::vector<Prim> cand;
   FwdCache fwd_cache(d->n_xforms);
-  const bool cubes_ok = cube_face_families(d, A);
+  bool cubes_ok = cube_face_families(d, A);
+  if (cubes_ok && A.n_cube_dirs > 0) {
+    size_t eligible = 0;
+    for (int32_t k = 0; k < n;) {
+      const rtc_node& nk = d->nodes[k];
+      if (nk.kind == RTC_CSG) { k = nk.skip; continue; }
+      if (nk.kind != RTC_GROUP && nk.kind != RTC_PLANE && nk.kind != RTC_CONE) eligible++;
+      k++;
+    }
+    if (eligible > CUBE_BVH_MAX_PRIMS) { cubes_ok = false; A.n_cube_dirs = 0; }
+  }
+  if (std::getenv("RTC_TIMING")) std::fprintf(stderr, "build_accel: %d cube face families, cubes %s\n", A.n_cube_dirs, cubes_ok ? "may enter the BVH" : "stay every-ray prims");
   struct Open { int32_t end, node; };
   std::vector<Open> groups;
   int32_t i = 0;
@@ -741,7 +721,6 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A, size_t device_mi
   const auto t1 = std::chrono::steady_clock::now();
   Builder b(cand, A, d);
   b.build();
-  mark_cube_subtrees(A);
   if (std::getenv("RTC_TIMING")) {
     const auto t2 = std::chrono::steady_clock::now();
     std::fprintf(stderr, "build_accel: walk+boxes+parents %.1f ms, BVH over %zu prims %.1f ms (%d threads)\n",

@@ -112,8 +112,8 @@ __global__ void __launch_bounds__(128, MINB) wave_stream_kernel(SceneView S, Cam
   uint32_t parent = 0, slot = 0;  // of this lane's item
   uint32_t pub_a = NONE, pub_b = NONE, pub_ri = 0;  // items this lane has written but not published yet
 
-  auto give_up = [&]() {  // something that must arrive did not: let the host render the frame recursively
-    atomicAdd(counters + 6, 1ull);
+  auto give_up = [&](unsigned long long why) {  // let the host render the frame recursively (why: 1 a queue is full, 2^32 a colour never arrived)
+    atomicAdd(counters + 6, why);
     atomicAdd(counters + 7, 1ull);
   };
   // A finished call's colour goes to its parent: the thread that arrives last at a parent evaluates it and carries the
@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(128, MINB) wave_stream_kernel(SceneView S, Cam
         unsigned long long ox = ld_relaxed_u64(theirs), oy = ld_relaxed_u64(theirs + 1), oz = ld_relaxed_u64(theirs + 2);
         uint32_t spins = 0;
         while (ox == WAVE_SENTINEL || oy == WAVE_SENTINEL || oz == WAVE_SENTINEL) {
-          if (++spins > (1u << 22)) { give_up(); return; }
+          if (++spins > (1u << 20)) { give_up(1ull << 32); return; }
           __nanosleep(40u);
           ox = ld_relaxed_u64(theirs); oy = ld_relaxed_u64(theirs + 1); oz = ld_relaxed_u64(theirs + 2);
         }
@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(128, MINB) wave_stream_kernel(SceneView S, Cam
     const uint32_t cap = A.lv[l + 1].cap_items;
     if (rec0 + (uint32_t)__popc(m) > A.lv[l].cap_recs || (unsigned long long)front0 + g_refl + back0 + g_refr > cap) {
       // the group does not fit: the frame is going to be re-rendered; tell every warp now (they are polling)
-      if ((int)lane == leader) give_up();
+      if ((int)lane == leader) give_up(1ull);
       return;
     }
     double2* R = reinterpret_cast<double2*>(A.lv[l].recs + ri);

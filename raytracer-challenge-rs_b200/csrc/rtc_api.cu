@@ -565,6 +565,9 @@ int resolve_wave(rtc_scene* s, cudaStream_t stream) {
   CUDA_TRY(cudaMemcpyAsync(&dropped, s->d_counters + 6, sizeof dropped, cudaMemcpyDeviceToHost, stream));
   CUDA_TRY(cudaStreamSynchronize(stream));
   if (!dropped) return RTC_OK;
+  if (std::getenv("RTC_TIMING"))
+    std::fprintf(stderr, "wavefront abandoned: %llu full-queue events, %llu colours that never arrived; rendering the frame recursively\n",
+                 dropped & 0xffffffffull, dropped >> 32);
   s->stat_flags |= RTC_STAT_WAVE_FALLBACK;
   s->wave_clean_px = 0;  // the abandoned frame left colours in child slots
   CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, (N_COUNTERS - 1) * sizeof(unsigned long long), stream));

