@@ -320,6 +320,8 @@ def main():
         dist.broadcast_object_list(name, src=0)
         if rank != 0:
             shared = mg.SharedHostCanvas(pkg, name[0], H * W * 3, local_rank, create=False)
+        shared.place(W, H, args.tile_rows, rank, world_size)   # each rank's tiles on its GPU's NUMA node, then pin
+        dist.barrier()
         host_ptr, host_np = shared.ptr, shared.numpy().reshape(H, W, 3)
         dist.barrier()
     e2e_fallbacks = [0]

@@ -253,9 +253,17 @@ RTC_API void rtc_canvas_destroy(rtc_canvas* canvas);
  *     rtc_render(scene, camera, opts{rank, nranks, tile_rows}, rtc_host_canvas_ptr(canvas), stats)
  * and ITS tiles reach the canvas over ITS OWN PCIe link (kernel stores straight into the mapping, or one strided DMA
  * of the rank's tiles for the wavefront renderer) — N links instead of rank 0's one. `create` != 0: create and size the
- * segment (rank 0; removed again by its rtc_host_canvas_destroy); 0: open an existing one. */
+ * segment (rank 0; removed again by its rtc_host_canvas_destroy); 0: open an existing one. Nothing is touched or
+ * page-locked yet (see rtc_host_canvas_place). */
 typedef struct rtc_host_canvas rtc_host_canvas;
 RTC_API int rtc_host_canvas_create(const char* name, size_t n_doubles, int device, int create, rtc_host_canvas** out);
+/* Optional, between create/open and the first rtc_host_canvas_ptr, on every rank, followed by a barrier of the caller's:
+ * put the pages of THIS rank's tiles on the NUMA node its GPU hangs off (mbind + first touch), so that eight GPUs do not
+ * all write across one socket's memory controllers and the inter-socket link (measured at 8 GPUs: 14 GB/s per rank into
+ * a canvas that lives on one node, against 50 GB/s at 4). Best effort: without NUMA (or without the right) it only
+ * zero-fills the tiles. The segment is page-locked for the GPU at the first rtc_host_canvas_ptr. */
+RTC_API int rtc_host_canvas_place(rtc_host_canvas* canvas, uint32_t hsize, uint32_t vsize, uint32_t tile_rows, uint32_t rank,
+                                  uint32_t nranks);
 RTC_API double* rtc_host_canvas_ptr(rtc_host_canvas* canvas);
 /* Frame hand-over through the segment itself (the mpsc channel of camera.rs:195-207): a rank that has rendered its
  * tiles of frame `frame` (1, 2, 3 …; rtc_render has returned, so they are in host memory) arrives; wait returns

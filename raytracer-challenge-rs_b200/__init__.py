@@ -122,6 +122,7 @@ def cuda_lib():
         lib.rtc_canvas_destroy.argtypes = [vp]
         lib.rtc_canvas_destroy.restype = None
         lib.rtc_host_canvas_create.argtypes = [C.c_char_p, sz, C.c_int, C.c_int, C.POINTER(vp)]
+        lib.rtc_host_canvas_place.argtypes = [vp, u32, u32, u32, u32, u32]
         lib.rtc_host_canvas_ptr.argtypes = [vp]
         lib.rtc_host_canvas_ptr.restype = vp
         lib.rtc_host_canvas_arrive.argtypes = [vp, u32, u32]

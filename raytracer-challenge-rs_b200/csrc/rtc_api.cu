@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstdio>
+#include <cctype>
 #include <cerrno>
 #include <cstring>
 #include <mutex>
@@ -16,6 +17,7 @@
 
 #include <fcntl.h>
 #include <sys/mman.h>
+#include <sys/syscall.h>
 #include <sys/stat.h>
 #include <unistd.h>
 
@@ -1256,18 +1258,57 @@ int rtc_host_canvas_create(const char* name, size_t n_doubles, int device, int c
   }
   rtc_host_canvas* c = new rtc_host_canvas();
   c->name = name; c->ptr = (double*)p; c->bytes = bytes; c->device = device; c->creator = create != 0;
-  if (create) std::memset(p, 0, bytes);  // touch every page before it is locked
-  cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped);
-  if (e != cudaSuccess) {
-    const std::string m = std::string("cudaHostRegister(host canvas): ") + cudaGetErrorString(e);
-    rtc_host_canvas_destroy(c);
-    return fail(RTC_ERR_CUDA, m);
-  }
-  c->registered = true;
   *out = c;
   return RTC_OK;
 }
-double* rtc_host_canvas_ptr(rtc_host_canvas* c) { return c ? c->ptr : nullptr; }
+// NUMA node of a CUDA device from sysfs (-1: unknown / no NUMA)
+static int gpu_numa_node(int device) {
+  char bdf[32] = {0};
+  if (cudaDeviceGetPCIBusId(bdf, sizeof bdf, device) != cudaSuccess) { cudaGetLastError(); return -1; }
+  for (char* q = bdf; *q; q++) *q = (char)std::tolower((unsigned char)*q);
+  const std::string path = std::string("/sys/bus/pci/devices/") + bdf + "/numa_node";
+  FILE* f = std::fopen(path.c_str(), "r");
+  if (!f) return -1;
+  int node = -1;
+  if (std::fscanf(f, "%d", &node) != 1) node = -1;
+  std::fclose(f);
+  return node;
+}
+int rtc_host_canvas_place(rtc_host_canvas* c, uint32_t hsize, uint32_t vsize, uint32_t tile_rows, uint32_t rank, uint32_t nranks) {
+  if (!c || c->registered || tile_rows == 0 || nranks == 0 || rank >= nranks) return fail(RTC_ERR_INVALID, "bad host canvas placement (before the first rtc_host_canvas_ptr only)");
+  if ((size_t)hsize * vsize * 3 * sizeof(double) > c->bytes - HOST_CANVAS_CTRL) return fail(RTC_ERR_INVALID, "canvas too small for the frame");
+  const int node = gpu_numa_node(c->device);
+  const size_t row_bytes = (size_t)hsize * 3 * sizeof(double), page = 4096;
+  char* base = reinterpret_cast<char*>(c->ptr);
+  for (uint32_t t = rank; (size_t)t * tile_rows < vsize; t += nranks) {
+    const size_t y0 = (size_t)t * tile_rows, y1 = std::min<size_t>(y0 + tile_rows, vsize);
+    size_t b0 = y0 * row_bytes, b1 = y1 * row_bytes;
+    if (node >= 0 && node < 64) {
+      // whole pages inside the tile (a page shared with a neighbouring tile goes wherever it is touched first)
+      const size_t p0 = (b0 + page - 1) & ~(page - 1), p1 = b1 & ~(page - 1);
+      if (p1 > p0) {
+        unsigned long mask = 1ul << node;
+        (void)syscall(SYS_mbind, base + p0, p1 - p0, 2 /* MPOL_BIND */, &mask, 65ul, 0u);  // best effort
+      }
+    }
+    std::memset(base + b0, 0, b1 - b0);  // first touch
+  }
+  if (rank == 0) std::memset(base + c->bytes - HOST_CANVAS_CTRL, 0, HOST_CANVAS_CTRL);
+  return RTC_OK;
+}
+double* rtc_host_canvas_ptr(rtc_host_canvas* c) {
+  if (!c) return nullptr;
+  if (!c->registered) {
+    if (cudaSetDevice(c->device) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    cudaError_t e = cudaHostRegister(c->ptr, c->bytes, cudaHostRegisterPortable | cudaHostRegisterMapped);
+    if (e != cudaSuccess) {
+      fail(RTC_ERR_CUDA, std::string("cudaHostRegister(host canvas): ") + cudaGetErrorString(e));
+      return nullptr;
+    }
+    c->registered = true;
+  }
+  return c->ptr;
+}
 static volatile uint32_t* host_canvas_word(rtc_host_canvas* c, uint32_t rank) {
   return reinterpret_cast<volatile uint32_t*>(reinterpret_cast<char*>(c->ptr) + c->bytes - HOST_CANVAS_CTRL + 64 * (size_t)rank);
 }

@@ -71,13 +71,26 @@ def gather_tiles(dist, canvas_rows, rank, nranks, tile_rows, recv=None):
 
 
 class SharedHostCanvas:
-    """rtc_host_canvas: one POSIX shm segment, page-locked and mapped for this process's GPU."""
+    """rtc_host_canvas: one POSIX shm segment mapped by every rank. create/open → place() on every rank → the caller's
+    barrier → .ptr (page-locks and maps the segment for this process's GPU)."""
 
     def __init__(self, pkg, name, n_doubles, device, create):
         self.pkg, self.n = pkg, n_doubles
         self.h = C.c_void_p()
+        self._ptr = None
         pkg._check(pkg.cuda_lib().rtc_host_canvas_create(name.encode(), n_doubles, device, 1 if create else 0, C.byref(self.h)))
-        self.ptr = pkg.cuda_lib().rtc_host_canvas_ptr(self.h)
+
+    def place(self, hsize, vsize, tile_rows, rank, nranks):
+        """This rank's tiles onto the NUMA node of its GPU (best effort) and zero-filled; before the first .ptr."""
+        self.pkg._check(self.pkg.cuda_lib().rtc_host_canvas_place(self.h, hsize, vsize, tile_rows, rank, nranks))
+
+    @property
+    def ptr(self):
+        if self._ptr is None:
+            self._ptr = self.pkg.cuda_lib().rtc_host_canvas_ptr(self.h)
+            if not self._ptr:
+                raise self.pkg.RtcError(-2, (self.pkg.cuda_lib().rtc_last_error() or b"").decode())
+        return self._ptr
 
     def numpy(self):
         return np.ctypeslib.as_array((C.c_double * self.n).from_address(self.ptr))

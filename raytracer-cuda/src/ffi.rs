@@ -195,6 +195,7 @@ extern "C" {
     pub fn rtc_canvas_push_tiles(canvas: *mut rtc_canvas, local_dev: *const f64, hsize: u32, vsize: u32, tile_rows: u32, rank: u32, nranks: u32, stream: *mut c_void) -> c_int;
     pub fn rtc_canvas_destroy(canvas: *mut rtc_canvas);
     pub fn rtc_host_canvas_create(name: *const c_char, n_doubles: usize, device: c_int, create: c_int, out: *mut *mut rtc_host_canvas) -> c_int;
+    pub fn rtc_host_canvas_place(canvas: *mut rtc_host_canvas, hsize: u32, vsize: u32, tile_rows: u32, rank: u32, nranks: u32) -> c_int;
     pub fn rtc_host_canvas_ptr(canvas: *mut rtc_host_canvas) -> *mut f64;
     pub fn rtc_host_canvas_arrive(canvas: *mut rtc_host_canvas, rank: u32, frame: u32) -> c_int;
     pub fn rtc_host_canvas_wait(canvas: *mut rtc_host_canvas, nranks: u32, frame: u32, timeout_s: f64) -> c_int;

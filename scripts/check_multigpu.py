@@ -84,6 +84,8 @@ for label, world_, cam in cases:
     dist.barrier()
     if rank != 0:
         canvas = mg.SharedHostCanvas(pkg, shm[0], n, local, create=False)
+    canvas.place(cam.hsize, cam.vsize, 8, rank, world)
+    dist.barrier()
     ds = pkg.DeviceScene(flat, device=local)
     cam_rtc = pkg.camera_to_rtc(cam)
     opts = pkg.make_opts(tile_rows=8, rank=rank, nranks=world)
