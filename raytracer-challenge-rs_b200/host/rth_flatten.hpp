@@ -73,6 +73,8 @@ class Flattener {
     size_t n_nodes = w.objects.size();
     for (const ShapeP& s : w.objects) n_nodes += count_below(*s);
     out_.nodes.reserve(n_nodes);
+    class_reserve(n_nodes);
+    class_reps_.reserve(n_nodes);
     if (n_nodes > 4096) {
       out_.tri_geom.reserve(9 * n_nodes);
       out_.tri_normals.reserve(9 * n_nodes);
@@ -175,13 +177,14 @@ class Flattener {
   // exact-bit equality class of a leaf: an open-addressing table keyed by a hash of everything the
   // reference's PartialEq compares; a hash match is confirmed field by field against the earlier shape,
   // so classes are exact and a million-triangle mesh costs no per-leaf allocation.
-  struct ClassEntry {
-    const Shape* s = nullptr;
-    int32_t xf = 0, mat = 0, id = 0;
+  struct ClassSlot {      // 16 bytes: a 2 M-slot table for a million-triangle mesh is 32 MB, one cache miss per leaf
     uint64_t hash = 0;
+    int32_t id = -1;      // -1: empty
+    int32_t _pad = 0;
   };
-  std::vector<ClassEntry> class_slots_;
-  size_t class_count_ = 0;
+  struct ClassRep { const Shape* s; int32_t xf, mat; };  // the first shape of every class, by class id
+  std::vector<ClassSlot> class_slots_;
+  std::vector<ClassRep> class_reps_;
 
   static uint64_t mix(uint64_t h, const void* p, size_t n) {
     const unsigned char* c = (const unsigned char*)p;
@@ -204,7 +207,7 @@ class Flattener {
     bb[3] = s.box.max.x; bb[4] = s.box.max.y; bb[5] = s.box.max.z;
   }
   static bool same_bits(const void* a, const void* b, size_t n) { return std::memcmp(a, b, n) == 0; }
-  static bool same_class(const Shape& a, int32_t axf, int32_t amat, const ClassEntry& e) {
+  static bool same_class(const Shape& a, int32_t axf, int32_t amat, const ClassRep& e) {
     const Shape& b = *e.s;
     if (a.kind != b.kind || axf != e.xf || amat != e.mat || a.shadow != b.shadow) return false;
     if (!same_bits(a.xf->m.m, b.xf->m.m, sizeof a.xf->m.m)) return false;
@@ -219,42 +222,51 @@ class Flattener {
     if (a.tri && !same_bits(a.tri.get(), b.tri.get(), sizeof(TriData))) return false;
     return true;
   }
-  void class_grow() {
-    std::vector<ClassEntry> old;
+  // table of at least 2 x `leaves` slots (a power of two), sized once: growing by doubling re-inserts every class
+  // eleven times over for a million leaves
+  void class_reserve(size_t leaves) {
+    size_t want = 1024;
+    while (want < 2 * leaves + 2) want <<= 1;
+    if (want <= class_slots_.size()) return;
+    std::vector<ClassSlot> old;
     old.swap(class_slots_);
-    class_slots_.assign(old.empty() ? 1024 : old.size() * 2, ClassEntry());
-    const size_t mask = class_slots_.size() - 1;
-    for (const ClassEntry& e : old) {
-      if (!e.s) continue;
+    class_slots_.assign(want, ClassSlot());
+    const size_t mask = want - 1;
+    for (const ClassSlot& e : old) {
+      if (e.id < 0) continue;
       size_t k = (size_t)e.hash & mask;
-      while (class_slots_[k].s) k = (k + 1) & mask;
+      while (class_slots_[k].id >= 0) k = (k + 1) & mask;
       class_slots_[k] = e;
     }
   }
   int32_t class_id(const Shape& s, int32_t xf, int32_t mat) {
-    if ((class_count_ + 1) * 2 > class_slots_.size()) class_grow();
+    if ((class_reps_.size() + 1) * 2 > class_slots_.size()) class_reserve(class_reps_.size() * 2 + 512);
     const int32_t head[4] = {s.kind, xf, mat, s.shadow ? 1 : 0};
     uint64_t h = mix(0x243F6A8885A308D3ull, head, sizeof head);
-    h = mix(h, s.xf->m.m, sizeof s.xf->m.m);
-    double bb[6];
-    box6(s, bb);
-    h = mix(h, bb, sizeof bb);
-    if (s.kind == RTC_CYLINDER || s.kind == RTC_CONE) {
-      const double lim[3] = {s.minimum, s.maximum, s.closed ? 1.0 : 0.0};
-      h = mix(h, lim, sizeof lim);
+    if (s.tri) {
+      // a mesh is a million of these: the three vertices tell triangles apart (same_class compares everything)
+      h = mix(h, &s.tri->p1, 3 * sizeof(Vec3));
+    } else {
+      h = mix(h, s.xf->m.m, sizeof s.xf->m.m);
+      double bb[6];
+      box6(s, bb);
+      h = mix(h, bb, sizeof bb);
+      if (s.kind == RTC_CYLINDER || s.kind == RTC_CONE) {
+        const double lim[3] = {s.minimum, s.maximum, s.closed ? 1.0 : 0.0};
+        h = mix(h, lim, sizeof lim);
+      }
     }
-    if (s.tri) h = mix(h, s.tri.get(), sizeof(TriData));
     const size_t mask = class_slots_.size() - 1;
     size_t k = (size_t)h & mask;
-    while (class_slots_[k].s) {
-      if (class_slots_[k].hash == h && same_class(s, xf, mat, class_slots_[k])) return class_slots_[k].id;
+    while (class_slots_[k].id >= 0) {
+      if (class_slots_[k].hash == h && same_class(s, xf, mat, class_reps_[(size_t)class_slots_[k].id])) return class_slots_[k].id;
       k = (k + 1) & mask;
     }
-    ClassEntry e;
-    e.s = &s; e.xf = xf; e.mat = mat; e.id = (int32_t)class_count_; e.hash = h;
-    class_slots_[k] = e;
-    class_count_++;
-    return e.id;
+    const int32_t id = (int32_t)class_reps_.size();
+    class_slots_[k].hash = h;
+    class_slots_[k].id = id;
+    class_reps_.push_back(ClassRep{&s, xf, mat});
+    return id;
   }
 
   void emit(const Shape& s) {
@@ -266,7 +278,13 @@ class Flattener {
     if (s.kind == RTC_GROUP) {
       out_.n_groups++;
       nd.aux = box_id(s.box);
-      for (const ShapeP& c : s.children) emit(*c);
+      // the children are separate heap objects (and a triangle's geometry one more): ask for them a few ahead
+      const size_t nc = s.children.size();
+      for (size_t i = 0; i < nc; i++) {
+        if (i + 8 < nc) __builtin_prefetch(s.children[i + 8].get());
+        if (i + 4 < nc && s.children[i + 4]->tri) __builtin_prefetch(s.children[i + 4]->tri.get());
+        emit(*s.children[i]);
+      }
       nd.skip = (int32_t)out_.nodes.size();
     } else if (s.kind == RTC_CSG) {
       out_.n_csg++;
