@@ -34,8 +34,39 @@ constexpr int BVH_STACK = 64;  // build bounds the depth (SAH to depth 40, then 
 
 struct BvhStack {
   int32_t node[BVH_STACK];
-  double tmin[BVH_STACK];
+  bvh_real tmin[BVH_STACK];
 };
+
+#if RTK_BVH_F32
+RTC_HD float rt_fmaf(float a, float b, float c) {
+#if defined(__CUDA_ARCH__)
+  return __fmaf_rn(a, b, c);
+#else
+  return fmaf(a, b, c);
+#endif
+}
+
+// The single-precision slab test of one of OUR boxes. t = lo*inv - o*inv as ONE fused multiply-add per plane:
+// `i*` = fl32(1/d), `c*` = fl32(-o/d). Against the exact entry/exit parameters of the (already outward-rounded) box the
+// computed ones are off by at most (|lo| + |o| + |lo - o|)*|1/d|*2^-24 per plane (one rounding each in i, c and the
+// fma); `e*` = (R + |o|)*|1/d|*5e-7 with R the tree's largest |coordinate| on that axis is four times that, so
+// [tmin, tmax] CONTAINS the true interval: a box the exact test would enter is never missed and tmin never exceeds the
+// true entry parameter. The caller guarantees |i|, |c|, R <= 1e15 (no overflow, hence no NaN).
+struct Slab32 {
+  float ix, iy, iz, cx, cy, cz, ex, ey, ez;
+  RTC_HD bool test(float lx, float ly, float lz, float hx, float hy, float hz, float& tmin, float& tmax) const {
+    const float ax = rt_fmaf(lx, ix, cx), bx = rt_fmaf(hx, ix, cx);
+    const float ay = rt_fmaf(ly, iy, cy), by = rt_fmaf(hy, iy, cy);
+    const float az = rt_fmaf(lz, iz, cz), bz = rt_fmaf(hz, iz, cz);
+    const float x0 = fminf(ax, bx) - ex, x1 = fmaxf(ax, bx) + ex;
+    const float y0 = fminf(ay, by) - ey, y1 = fmaxf(ay, by) + ey;
+    const float z0 = fminf(az, bz) - ez, z1 = fmaxf(az, bz) + ez;
+    tmin = fmaxf(fmaxf(x0, y0), z0);
+    tmax = fminf(fminf(x1, y1), z1);
+    return !(tmin > tmax);
+  }
+};
+#endif
 
 // Has `ray` passed the box of every reference Group enclosing `node`? `ok_group`: innermost group
 // already validated for this ray (its ancestors are then valid too), -1 initially (= top level).
@@ -158,9 +189,35 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
     int32_t ok_group = -1;
     RayD lr;
     int32_t lr_xf = -1;
+#if !RTK_BVH_F32
     V3 inv = v3(0.0, 0.0, 0.0);
-    bool have_inv = false, plain = false;
+    bool plain = false;
+#endif
+    bool have_inv = false;
     int sp = 0;
+#if RTK_BVH_F32
+    // what a query carries through the traversal: nine floats and two flags (the double-precision reciprocal direction
+    // is recomputed per node on the rare slow path instead of living in twelve registers)
+    Slab32 F;
+    F.ix = F.iy = F.iz = F.cx = F.cy = F.cz = F.ex = F.ey = F.ez = 0.0f;
+    bool fast32 = false, zero_inv = false;
+    auto plain_dir = [&]() {
+      return ray.d.x != 0.0 && ray.d.y != 0.0 && ray.d.z != 0.0 && ray.d.x == ray.d.x && ray.d.y == ray.d.y && ray.d.z == ray.d.z;
+    };
+    // Query::cull in single precision. tmin / tmax are outer bounds of the box's parameter interval; the query's own
+    // slack (1e-6 relative) is doubled to absorb the rounding of the limit and of these few float operations.
+    // `lim32` follows C.limit, which only moves while leaves are tested: refreshed after every leaf phase.
+    float lim32 = HUGE_VALF;
+    auto cull32 = [&](float tmin, float tmax) -> bool {
+      if (C.mode == Q_NEG) return tmin > 2e-6f * (1.0f + fabsf(tmin));
+      return tmax < -2e-6f * (1.0f + fabsf(tmax)) || tmin > lim32;
+    };
+#define RTK_BVH_CULL(tmin, tmax) cull32((tmin), (tmax))
+#define RTK_BVH_TINF HUGE_VALF
+#else
+#define RTK_BVH_CULL(tmin, tmax) C.cull((tmin), (tmax))
+#define RTK_BVH_TINF rt_inf()
+#endif
     // -DRTK_SHARED_STACK=n (A/B of the "per-warp shared-memory stack" of the brief): the first n entries of the traversal
     // stack live in shared memory ([entry][thread]: conflict-free), the rest in the thread's local BvhStack.
 #if defined(RTK_SHARED_STACK) && defined(__CUDA_ARCH__)
@@ -375,9 +432,18 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
         }
       }
       if (C.done() || S.n_bvh <= 0) return;
+#if RTK_BVH_F32
+      lim32 = (float)(C.limit + 2e-6 * (1.0 + fabs(C.limit)));
+#endif
       if (!have_inv) {  // the always-run is done: enter the BVH at its root
-        inv = v3(1.0 / ray.d.x, 1.0 / ray.d.y, 1.0 / ray.d.z);
+#if RTK_BVH_F32
+        V3 inv;
+        bool plain;
+        plain = plain_dir();
+#else
         plain = ray.d.x != 0.0 && ray.d.y != 0.0 && ray.d.z != 0.0 && ray.d.x == ray.d.x && ray.d.y == ray.d.y && ray.d.z == ray.d.z;
+#endif
+        inv = v3(1.0 / ray.d.x, 1.0 / ray.d.y, 1.0 / ray.d.z);
         have_inv = true;
         if constexpr (!NO_GENERIC) {
           // a ray EPSILON-parallel to a face family of a cube in the BVH (CubeDir): no box bounds that cube's hits for
@@ -398,13 +464,30 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
           }
           }
           if (cube_near) { inv = v3(0.0, 0.0, 0.0); plain = false; }
+#if RTK_BVH_F32
+          zero_inv = cube_near;
+#endif
         }
+#if RTK_BVH_F32
+        {
+          const double rx = S.bvh_ext[0], ry = S.bvh_ext[1], rz = S.bvh_ext[2];  // every box's |coordinate| bound
+          const double cx = -(ray.o.x * inv.x), cy = -(ray.o.y * inv.y), cz = -(ray.o.z * inv.z);
+          const double big = 1e15;
+          fast32 = plain && fabs(inv.x) <= big && fabs(inv.y) <= big && fabs(inv.z) <= big && fabs(cx) <= big && fabs(cy) <= big &&
+                   fabs(cz) <= big && rx <= big && ry <= big && rz <= big;
+          F.ix = (float)inv.x; F.iy = (float)inv.y; F.iz = (float)inv.z;
+          F.cx = (float)cx; F.cy = (float)cy; F.cz = (float)cz;
+          F.ex = (float)((rx + fabs(ray.o.x)) * fabs(inv.x) * 5e-7);
+          F.ey = (float)((ry + fabs(ray.o.y)) * fabs(inv.y) * 5e-7);
+          F.ez = (float)((rz + fabs(ray.o.z)) * fabs(inv.z) * 5e-7);
+        }
+#endif
         cur = 0;
       } else {
         cur = NONE;
         while (sp > 0) {
           sp--;
-          if (!C.cull(RTK_ST_TMIN(sp), rt_inf())) { cur = RTK_ST_NODE(sp); break; }
+          if (!RTK_BVH_CULL(RTK_ST_TMIN(sp), RTK_BVH_TINF)) { cur = RTK_ST_NODE(sp); break; }
         }
         if (cur == NONE) return;
       }
@@ -412,6 +495,39 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
       while (cur >= 0) {
         const BvhNode* bn = S.bvh + cur;
         RTK_COUNT(bvh_nodes, 1);
+#if RTK_BVH_F32
+#if defined(__CUDA_ARCH__)
+        // the whole 64-byte node in four 16-byte loads
+        const float4* bq = reinterpret_cast<const float4*>(bn);
+        const float4 q0 = __ldg(bq), q1 = __ldg(bq + 1), q2 = __ldg(bq + 2);
+        const int4 ci = __ldg(reinterpret_cast<const int4*>(bq + 3));
+        const int32_t c0 = ci.x, n0 = ci.y, c1 = ci.z, n1 = ci.w;
+        const float l0x = q0.x, l0y = q0.y, l0z = q0.z, h0x = q0.w, h0y = q1.x, h0z = q1.y;
+        const float l1x = q1.z, l1y = q1.w, l1z = q2.x, h1x = q2.y, h1y = q2.z, h1z = q2.w;
+#else
+        const int32_t c0 = bn->c0, n0 = bn->n0, c1 = bn->c1, n1 = bn->n1;
+        const float l0x = bn->lo0[0], l0y = bn->lo0[1], l0z = bn->lo0[2], h0x = bn->hi0[0], h0y = bn->hi0[1], h0z = bn->hi0[2];
+        const float l1x = bn->lo1[0], l1y = bn->lo1[1], l1z = bn->lo1[2], h1x = bn->hi1[0], h1y = bn->hi1[1], h1z = bn->hi1[2];
+#endif
+        float t0min = 0.0f, t0max = 0.0f, t1min = 0.0f, t1max = 0.0f;
+        bool h0, h1;
+        if (fast32) {
+          const bool b0 = F.test(l0x, l0y, l0z, h0x, h0y, h0z, t0min, t0max);
+          const bool b1 = F.test(l1x, l1y, l1z, h1x, h1y, h1z, t1min, t1max);
+          h0 = n0 >= 0 && b0 && !cull32(t0min, t0max);
+          h1 = n1 >= 0 && b1 && !cull32(t1min, t1max);
+        } else {
+          // a zero / NaN / extreme direction component, or a cube-parallel ray (inv == 0): the double-precision test
+          const bool plain = !zero_inv && plain_dir();
+          const V3 inv = zero_inv ? v3(0.0, 0.0, 0.0) : v3(1.0 / ray.d.x, 1.0 / ray.d.y, 1.0 / ray.d.z);
+          double d0min = 0.0, d0max = 0.0, d1min = 0.0, d1max = 0.0;
+          h0 = n0 >= 0 && own_box(l0x, l0y, l0z, h0x, h0y, h0z, ray, inv, plain, d0min, d0max) && !C.cull(d0min, d0max);
+          h1 = n1 >= 0 && own_box(l1x, l1y, l1z, h1x, h1y, h1z, ray, inv, plain, d1min, d1max) && !C.cull(d1min, d1max);
+          // (for the stack and the near/far order: at or below the double; a NaN or inf stays what it is)
+          t0min = bvh_below(d0min);
+          t1min = bvh_below(d1min);
+        }
+#else
 #if defined(__CUDA_ARCH__)
         // the whole 128-byte node in seven 16-byte loads
         const double2* bq = reinterpret_cast<const double2*>(bn);
@@ -428,6 +544,7 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
         double t0min = 0.0, t0max = 0.0, t1min = 0.0, t1max = 0.0;
         const bool h0 = n0 >= 0 && own_box(l0x, l0y, l0z, h0x, h0y, h0z, ray, inv, plain, t0min, t0max) && !C.cull(t0min, t0max);
         const bool h1 = n1 >= 0 && own_box(l1x, l1y, l1z, h1x, h1y, h1z, ray, inv, plain, t1min, t1max) && !C.cull(t1min, t1max);
+#endif
         // refs: >= 0 inner node, < 0 leaf ~(first << 3 | count)
         const int32_t r0 = n0 > 0 ? ~((c0 << 3) | n0) : c0;
         const int32_t r1 = n1 > 0 ? ~((c1 << 3) | n1) : c1;
@@ -446,7 +563,7 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
         } else {
           while (sp > 0) {
             sp--;
-            if (!C.cull(RTK_ST_TMIN(sp), rt_inf())) { cur = RTK_ST_NODE(sp); break; }
+            if (!RTK_BVH_CULL(RTK_ST_TMIN(sp), RTK_BVH_TINF)) { cur = RTK_ST_NODE(sp); break; }
           }
         }
       }

@@ -34,13 +34,54 @@
 
 namespace rtk {
 
-struct BvhNode {     // 128 bytes: both children's boxes in one fetch
-  double lo0[3], hi0[3];
-  double lo1[3], hi1[3];
+// Our own boxes only have to be CONSERVATIVE (the reference never sees them), so they are stored in single precision,
+// rounded outward: a node is 64 bytes — both children's boxes and references in four 16-byte loads, two nodes to a
+// 128-byte line — and the slab test runs on the FP32 pipe (rt_accel.cuh: search). -DRTK_BVH_F32=0 keeps the 128-byte
+// double-precision node of rounds 1-2 for A/B runs.
+#if !defined(RTK_BVH_F32)
+#define RTK_BVH_F32 1
+#endif
+#if RTK_BVH_F32
+typedef float bvh_real;
+#else
+typedef double bvh_real;
+#endif
+
+struct BvhNode {
+  bvh_real lo0[3], hi0[3];
+  bvh_real lo1[3], hi1[3];
   int32_t c0, n0;    // n > 0: leaf, prims [c, c+n) of bvh_prims; n == 0: inner node index c; n < 0: empty
   int32_t c1, n1;
+#if !RTK_BVH_F32
   int32_t _pad[4];
+#endif
 };
+
+// the nearest bvh_real at or below / at or above x
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+inline bvh_real bvh_below(double x) {
+#if RTK_BVH_F32
+  float f = (float)x;
+  if ((double)f > x) f = nextafterf(f, -HUGE_VALF);
+  return f;
+#else
+  return x;
+#endif
+}
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+inline bvh_real bvh_above(double x) {
+#if RTK_BVH_F32
+  float f = (float)x;
+  if ((double)f < x) f = nextafterf(f, HUGE_VALF);
+  return f;
+#else
+  return x;
+#endif
+}
 
 struct PrimRec {     // 128 bytes: everything the every-ray loop needs about one prim, in one place
   int32_t node, aux, parent;
@@ -56,7 +97,12 @@ struct LeafRec {     // 96 bytes: one BVH prim (any bounded leaf shape), in BVH 
   int32_t aux, _pad;     // rtc_node.aux (cylinder: index into limits)
 };
 
-static_assert(sizeof(PrimRec) == 128 && sizeof(LeafRec) == 96 && sizeof(BvhNode) == 128, "record layout");
+// largest |coordinate| per axis of the tree: the root's first child spans it
+inline void bvh_extent(const BvhNode& root, double ext[3]) {
+  for (int a = 0; a < 3; a++) ext[a] = std::fmax(std::fabs((double)root.lo0[a]), std::fabs((double)root.hi0[a]));
+}
+
+static_assert(sizeof(PrimRec) == 128 && sizeof(LeafRec) == 96 && sizeof(BvhNode) == (RTK_BVH_F32 ? 64 : 128), "record layout");
 
 // World-space bounding sphere of an every-ray sphere prim (the first SPH_CULL_MAX of them; there are at
 // most BVH_MIN_PRIMS - 1 unless a transform is degenerate). Travels inside SceneView, i.e. in the
@@ -359,9 +405,9 @@ struct Builder {
   }
 
   void set_child(BvhNode& nd, int which, const Box& bx, int32_t c, int32_t n) {
-    double* lo = which ? nd.lo1 : nd.lo0;
-    double* hi = which ? nd.hi1 : nd.hi0;
-    for (int a = 0; a < 3; a++) { lo[a] = bx.lo[a]; hi[a] = bx.hi[a]; }
+    bvh_real* lo = which ? nd.lo1 : nd.lo0;
+    bvh_real* hi = which ? nd.hi1 : nd.hi0;
+    for (int a = 0; a < 3; a++) { lo[a] = bvh_below(bx.lo[a]); hi[a] = bvh_above(bx.hi[a]); }
     if (which) { nd.c1 = c; nd.n1 = n; } else { nd.c0 = c; nd.n0 = n; }
   }
 

@@ -4,7 +4,7 @@
 // boxes are part of the parity contract; OUR search tree is free (the search result never depends on it: ties resolve by
 // node index and every candidate is validated against the reference's group chain). The host builder
 // (rt_accel_build.hpp: binned SAH on up to 16 threads) takes ≈ 0.4 s for the million-triangle scene; here the same
-// 128-byte BvhNode / 96-byte LeafRec tables are produced by seven kernels and one radix sort, in milliseconds:
+// BvhNode / 96-byte LeafRec tables are produced by seven kernels and one radix sort, in milliseconds:
 //
 //   prim_box_kernel     world-space box of every BVH-eligible leaf from the tables already in the slab (triangles: three
 //                       transformed vertices; sphere / cube / bounded cylinder: the eight transformed corners of the
@@ -15,7 +15,7 @@
 //   cluster_box_kernel  four consecutive prims in Morton order form one leaf; its box
 //   sah_level_kernel    top-down, one launch per level, one warp per node: the node's run of the Morton order is cut
 //                       where the surface-area heuristic is cheapest among 31 equal-count cuts (two warp scans); child
-//                       boxes and references go straight into the 128-byte BvhNode; node 0 is the root
+//                       boxes (rounded outward to the node's precision) and references go straight into the BvhNode; node 0 is the root
 //   emit_kernel         LeafRec (node, transform, group parent, kind, inline triangle geometry) in leaf order
 //
 // (The plain radix tree over the Morton keys — Karras 2012 — was built first: 0.26 ms for 26 k prims, but 2.3x slower
@@ -223,8 +223,13 @@ __global__ void sah_level_kernel(const Range* __restrict__ in, int n_in, Range* 
     const int nl = cut - r.first, nr = r.count - nl;
     auto leaf_count = [&](int c) { const int first = c * LEAF_PRIMS; return n_prims - first < LEAF_PRIMS ? n_prims - first : LEAF_PRIMS; };
     BvhNode nd;
-    for (int a = 0; a < 3; a++) { nd.lo0[a] = lbox.lo[a]; nd.hi0[a] = lbox.hi[a]; nd.lo1[a] = rbox.lo[a]; nd.hi1[a] = rbox.hi[a]; }
+    for (int a = 0; a < 3; a++) {
+      nd.lo0[a] = bvh_below(lbox.lo[a]); nd.hi0[a] = bvh_above(lbox.hi[a]);
+      nd.lo1[a] = bvh_below(rbox.lo[a]); nd.hi1[a] = bvh_above(rbox.hi[a]);
+    }
+#if !RTK_BVH_F32
     nd._pad[0] = nd._pad[1] = nd._pad[2] = nd._pad[3] = 0;
+#endif
     int n_new = (nl > 1 ? 1 : 0) + (nr > 1 ? 1 : 0);
     int id = n_new ? atomicAdd(n_nodes, n_new) : 0;
     int slot = n_new ? atomicAdd(n_out, n_new) : 0;
@@ -311,11 +316,10 @@ inline cudaError_t build(const In& in, int32_t shift, BvhNode* nodes, LeafRec* r
     // by an all-covering extent
     BvhNode root;
     for (int a = 0; a < 3; a++) {
-      root.lo0[a] = -1.7976931348623157e308; root.hi0[a] = 1.7976931348623157e308;
-      root.lo1[a] = 1.7976931348623157e308; root.hi1[a] = -1.7976931348623157e308;
+      root.lo0[a] = bvh_below(-1.7976931348623157e308); root.hi0[a] = bvh_above(1.7976931348623157e308);
+      root.lo1[a] = bvh_above(1.7976931348623157e308); root.hi1[a] = bvh_below(-1.7976931348623157e308);
     }
     root.c0 = shift; root.n0 = n; root.c1 = 0; root.n1 = -1;
-    root._pad[0] = root._pad[1] = root._pad[2] = root._pad[3] = 0;
     DEVB_TRY(cudaMemcpyAsync(nodes, &root, sizeof root, cudaMemcpyHostToDevice, stream));
   }
   emit_kernel<<<blocks(n), T, 0, stream>>>(in, idx2, recs);

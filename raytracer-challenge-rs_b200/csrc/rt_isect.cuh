@@ -41,6 +41,7 @@ struct SceneView {
   CubeDir cube_dirs[CUBE_DIR_MAX]; // face families of the cubes in the BVH (EPSILON-parallel rule of cube.rs:30-48)
   int32_t n_cube_dirs;
   int32_t _pad_cube;
+  double bvh_ext[3];         // the BVH's largest |coordinate| per axis (error bound of the single-precision slab test)
 };
 
 RTC_HD void slab_axis(double origin, double direction, double mn, double mx, double& tmin, double& tmax) {

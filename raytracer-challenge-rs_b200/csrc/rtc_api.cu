@@ -844,6 +844,18 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   for (int k = 0; k < SPH_CULL_MAX; k++) v.sph_cull[k] = accel.sph_cull[k];
   for (int k = 0; k < CUBE_DIR_MAX; k++) v.cube_dirs[k] = accel.cube_dirs[k];
   v.n_cube_dirs = accel.n_cube_dirs;
+  v.bvh_ext[0] = v.bvh_ext[1] = v.bvh_ext[2] = 0.0;
+  if (n_bvh_nodes > 0) {
+    BvhNode root;
+    if (accel.deferred) {  // built on the device: fetch the root (the build has completed on s->stream)
+      cudaError_t e = cudaMemcpyAsync(&root, s->slab + parts[12].off, sizeof root, cudaMemcpyDeviceToHost, s->stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+      if (e != cudaSuccess) return bail(e, "device BVH root");
+    } else {
+      root = accel.bvh[0];
+    }
+    bvh_extent(root, v.bvh_ext);
+  }
   v.n_bvh = (int32_t)n_bvh_nodes;
   v.n_nodes = (int32_t)d->n_nodes;
   v.n_lights = (int32_t)d->n_lights;

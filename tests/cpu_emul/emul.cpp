@@ -45,6 +45,8 @@ void build_view(const rtc_scene_desc* d, Built& b) {
   for (int k = 0; k < SPH_CULL_MAX; k++) v.sph_cull[k] = b.accel.sph_cull[k];
   for (int k = 0; k < CUBE_DIR_MAX; k++) v.cube_dirs[k] = b.accel.cube_dirs[k];
   v.n_cube_dirs = b.accel.n_cube_dirs;
+  v.bvh_ext[0] = v.bvh_ext[1] = v.bvh_ext[2] = 0.0;
+  if (!b.accel.bvh.empty()) bvh_extent(b.accel.bvh[0], v.bvh_ext);
 }
 CameraD make_cam(const rtc_camera* c) {
   CameraD cam;
