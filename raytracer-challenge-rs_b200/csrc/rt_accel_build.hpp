@@ -262,7 +262,8 @@ struct Prim {
 };
 
 constexpr int SAH_BINS = 16;
-constexpr int LEAF_MAX = 4;
+constexpr double SAH_KT = 2.0;         // cost of visiting one node, in leaf tests
+constexpr double SAH_W_GENERIC = 3.0;  // cost of a generic leaf test (cube / cylinder / cone), in triangle tests
 
 struct Builder {
   std::vector<Prim>& prims;
@@ -295,7 +296,9 @@ struct Builder {
   // Split prims[b,e) — returns mid (b < mid < e), or -1 to make a leaf.
   int split(int b, int e, const Box& bounds, int depth, int nthreads) {
     const int n = e - b;
-    if (n <= LEAF_MAX) return -1;
+    if (n <= 1) return -1;
+    static const int leaf_max = [] { const char* e = std::getenv("RTC_LEAF_MAX"); int v = e ? std::atoi(e) : 0; return v < 0 ? 0 : (v > 7 ? 7 : v); }();
+    if (leaf_max > 0 && n <= leaf_max) return -1;  // experiments: a fixed leaf size instead of the SAH's own stop
     if (depth >= 40) {  // bound the traversal stack: median split along the widest axis from here on
       int a = 0;
       for (int k = 1; k < 3; k++)
@@ -377,6 +380,21 @@ struct Builder {
         double cost = acc.area() * c + right_area[k + 1] * right_cnt[k + 1];
         if (cost < best_cost) { best_cost = cost; best_axis = a; best_bin = k; }
       }
+    }
+    // The SAH's own stop. A leaf of n prims costs sum(w) leaf tests whenever its box is entered; splitting costs one more
+    // node visit (SAH_KT leaf tests' worth: a 64-byte node and two single-precision slab tests against a 96-byte record
+    // and a double-precision Moeller-Trumbore or quadratic) plus the children's expected tests. w = 1 for triangles
+    // and spheres, SAH_W_GENERIC for the kinds that go through the generic leaf test (cube, cylinder, cone).
+    if (leaf_max == 0 && n <= 7) {
+      static const double kt = [] { const char* e = std::getenv("RTC_SAH_KT"); return e ? std::atof(e) : SAH_KT; }();
+      static const double wg = [] { const char* e = std::getenv("RTC_SAH_WG"); return e ? std::atof(e) : SAH_W_GENERIC; }();
+      double wsum = 0.0;
+      for (int k = b; k < e; k++) {
+        const int32_t kind = desc->nodes[prims[(size_t)k].node].kind;
+        wsum += (kind == RTC_TRIANGLE || kind == RTC_SMOOTH_TRIANGLE || kind == RTC_SPHERE) ? 1.0 : wg;
+      }
+      const double area = bounds.area();
+      if (best_axis < 0 || !(kt * area + best_cost * (wsum / n) < wsum * area)) return -1;
     }
     int mid;
     if (best_axis < 0) {  // all centroids coincide: split in the middle

@@ -24,6 +24,12 @@ for name in sys.argv[2:] or ["teapot_standin", "cover", "primitives_csg", "mesh_
     for _ in range(8):
         _, st2 = ds.render(cam)
         ms2.append(st2.kernel_ms)
-    print("%s [%s] recursive %.3f ms (min %.3f)  default %.3f ms (launches %d)  sum %.9f" % (name, TAG, float(np.median(ms)), min(ms), float(np.median(ms2)), st2.launches, float(img.sum())), flush=True)
+    ms3 = []
+    for _ in range(8):
+        img3, st3 = ds.render(cam, wavefront=True)
+        ms3.append(st3.kernel_ms)
+    print("%s [%s] recursive %.3f ms (min %.3f)  default %.3f ms (launches %d)  levels %.3f ms (launches %d, flags %d, same %s)  sum %.9f" % (
+        name, TAG, float(np.median(ms)), min(ms), float(np.median(ms2)), st2.launches, float(np.median(ms3)), st3.launches, st3.flags,
+        np.array_equal(img3, img), float(img.sum())), flush=True)
     np.save("/tmp/il_%s_%s.npy" % (name, TAG), img)
     ds.close()
