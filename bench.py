@@ -446,7 +446,7 @@ def main():
             achieved = bytes_frame / (ms_per_step * 1e-3) / 1e9
             roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm * world_size, "unit": "GB/s", "frac": achieved / (hbm * world_size),
                         "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_frame": bytes_frame,
-                        "bytes_definition": "BVH nodes visited x 128 B + leaf prims tested x 96 B (device-counted per ray, profiles/algorithmic_bytes.json) x rays of this run + 24 B per pixel",
+                        "bytes_definition": "BVH nodes visited x 64 B + leaf prims tested x 96 B (device-counted per ray, profiles/algorithmic_bytes.json) x rays of this run + 24 B per pixel",
                         "fp64_peak_tflops_nofma": peak_nofma / 1e3 * world_size}
         elif flops_frame is not None:
             achieved = flops_frame / (ms_per_step * 1e-3) / 1e12

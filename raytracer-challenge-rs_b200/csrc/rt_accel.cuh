@@ -65,6 +65,17 @@ struct Slab32 {
     tmax = fminf(fminf(x1, y1), z1);
     return !(tmin > tmax);
   }
+  // The same with the error bound folded into the addend: the plane the ray meets first on an axis (the low one for a
+  // positive direction) gets c - e, the other c + e — one fma per plane and no min/max per axis. ((c -+ e) is rounded
+  // once more: (|c| + e)*2^-24, which the fourfold margin of e covers.)
+  RTC_HD bool test_nf(float nx, float ny, float nz, float fx, float fy, float fz, float& tmin, float& tmax) const {
+    const float x0 = rt_fmaf(nx, ix, cx - ex), x1 = rt_fmaf(fx, ix, cx + ex);
+    const float y0 = rt_fmaf(ny, iy, cy - ey), y1 = rt_fmaf(fy, iy, cy + ey);
+    const float z0 = rt_fmaf(nz, iz, cz - ez), z1 = rt_fmaf(fz, iz, cz + ez);
+    tmin = fmaxf(fmaxf(x0, y0), z0);
+    tmax = fminf(fminf(x1, y1), z1);
+    return !(tmin > tmax);
+  }
 };
 #endif
 
@@ -493,8 +504,88 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
       }
       // -- node phase: descend until this lane holds a leaf ref (cur < 0) or nothing (NONE)
       while (cur >= 0) {
-        const BvhNode* bn = S.bvh + cur;
+        const TravNode* bn = S.bvh + cur;
         RTK_COUNT(bvh_nodes, 1);
+#if RTK_BVH_WIDE
+        // ---- four children per node: one 128-byte line in seven 16-byte loads
+        float lx[4], ly[4], lz[4], hx[4], hy[4], hz[4];
+        int32_t rf[4];
+#if defined(__CUDA_ARCH__)
+        {
+          const float4* bq = reinterpret_cast<const float4*>(bn);
+          const float4 q0 = __ldg(bq), q1 = __ldg(bq + 1), q2 = __ldg(bq + 2), q3 = __ldg(bq + 3), q4 = __ldg(bq + 4), q5 = __ldg(bq + 5);
+          const int4 ri = __ldg(reinterpret_cast<const int4*>(bq + 6));
+          lx[0] = q0.x; lx[1] = q0.y; lx[2] = q0.z; lx[3] = q0.w;
+          ly[0] = q1.x; ly[1] = q1.y; ly[2] = q1.z; ly[3] = q1.w;
+          lz[0] = q2.x; lz[1] = q2.y; lz[2] = q2.z; lz[3] = q2.w;
+          hx[0] = q3.x; hx[1] = q3.y; hx[2] = q3.z; hx[3] = q3.w;
+          hy[0] = q4.x; hy[1] = q4.y; hy[2] = q4.z; hy[3] = q4.w;
+          hz[0] = q5.x; hz[1] = q5.y; hz[2] = q5.z; hz[3] = q5.w;
+          rf[0] = ri.x; rf[1] = ri.y; rf[2] = ri.z; rf[3] = ri.w;
+        }
+#else
+        for (int k = 0; k < 4; k++) {
+          lx[k] = bn->lox[k]; ly[k] = bn->loy[k]; lz[k] = bn->loz[k];
+          hx[k] = bn->hix[k]; hy[k] = bn->hiy[k]; hz[k] = bn->hiz[k];
+          rf[k] = bn->ref[k];
+        }
+#endif
+        // key: the child's entry parameter if it has to be visited, +inf if not
+        float key[4];
+        if (fast32) {
+          const bool sx = F.ix < 0.0f, sy = F.iy < 0.0f, sz = F.iz < 0.0f;
+#if defined(__CUDACC__)
+#pragma unroll
+#endif
+          for (int k = 0; k < 4; k++) {
+            float tmin, tmax;
+            const bool in = F.test_nf(sx ? hx[k] : lx[k], sy ? hy[k] : ly[k], sz ? hz[k] : lz[k],
+                                      sx ? lx[k] : hx[k], sy ? ly[k] : hy[k], sz ? lz[k] : hz[k], tmin, tmax);
+            key[k] = (rf[k] != BVH_EMPTY && in && !cull32(tmin, tmax)) ? tmin : HUGE_VALF;
+          }
+        } else {
+          // a zero / NaN / extreme direction component, or a cube-parallel ray (inv == 0): the double-precision test
+          const bool plain = !zero_inv && plain_dir();
+          const V3 inv = zero_inv ? v3(0.0, 0.0, 0.0) : v3(1.0 / ray.d.x, 1.0 / ray.d.y, 1.0 / ray.d.z);
+#if defined(__CUDACC__)
+#pragma unroll 1
+#endif
+          for (int k = 0; k < 4; k++) {
+            double dmin = 0.0, dmax = 0.0;
+            const bool in = rf[k] != BVH_EMPTY && own_box(lx[k], ly[k], lz[k], hx[k], hy[k], hz[k], ray, inv, plain, dmin, dmax) && !C.cull(dmin, dmax);
+            // at or below the double; a NaN entry parameter orders first (the child must not be dropped)
+            key[k] = in ? (dmin == dmin ? fminf(bvh_below(dmin), 3.0e38f) : -HUGE_VALF) : HUGE_VALF;
+          }
+        }
+        // ascending by key (five compare-exchanges): the nearest child is next, the other wanted ones go on the stack
+        // farthest first
+#define RTK_CSWAP(a, b) do { const bool sw = key[b] < key[a]; const float tk = sw ? key[b] : key[a]; key[b] = sw ? key[a] : key[b]; key[a] = tk; \
+                             const int32_t tr = sw ? rf[b] : rf[a]; rf[b] = sw ? rf[a] : rf[b]; rf[a] = tr; } while (0)
+        RTK_CSWAP(0, 1); RTK_CSWAP(2, 3); RTK_CSWAP(0, 2); RTK_CSWAP(1, 3); RTK_CSWAP(1, 2);
+#undef RTK_CSWAP
+        cur = NONE;
+        if (key[0] < HUGE_VALF) {
+          cur = rf[0];
+#if defined(__CUDACC__)
+#pragma unroll
+#endif
+          for (int k = 3; k >= 1; k--) {
+            if (key[k] < HUGE_VALF) {
+              if (sp < BVH_STACK) {
+                RTK_ST_PUSH(sp, rf[k], key[k]);
+                sp++;
+              } else {
+                *err |= ERR_OVERFLOW;
+              }
+            }
+          }
+        } else {
+          while (sp > 0) {
+            sp--;
+            if (!RTK_BVH_CULL(RTK_ST_TMIN(sp), RTK_BVH_TINF)) { cur = RTK_ST_NODE(sp); break; }
+          }
+        }
+#else  // ---- two children per node
 #if RTK_BVH_F32
 #if defined(__CUDA_ARCH__)
         // the whole 64-byte node in four 16-byte loads
@@ -566,6 +657,7 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
             if (!RTK_BVH_CULL(RTK_ST_TMIN(sp), RTK_BVH_TINF)) { cur = RTK_ST_NODE(sp); break; }
           }
         }
+#endif  // RTK_BVH_WIDE
       }
       if (cur == NONE) return;
       {

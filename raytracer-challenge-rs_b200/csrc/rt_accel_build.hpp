@@ -57,6 +57,24 @@ struct BvhNode {
 #endif
 };
 
+// What the kernels traverse (-DRTK_BVH_WIDE=0: the binary node itself): the binary tree collapsed to FOUR children per
+// node — half the dependent node fetches per ray, which is what a ray's search waits on. One node is one 128-byte line:
+// the children's boxes axis by axis (a 16-byte load per plane family) and one reference each.
+#if !defined(RTK_BVH_WIDE)
+#define RTK_BVH_WIDE 0
+#endif
+#if RTK_BVH_WIDE && !RTK_BVH_F32
+#error "RTK_BVH_WIDE needs RTK_BVH_F32"
+#endif
+constexpr int32_t BVH_EMPTY = -0x7fffffff - 1;
+constexpr int WIDE_STACK_MAX = 64;   // = BVH_STACK (rt_accel.cuh)
+struct BvhNode4 {
+  float lox[4], loy[4], loz[4], hix[4], hiy[4], hiz[4];
+  int32_t ref[4];    // >= 0: inner node; < 0: leaf ~(first << 3 | count), prims [first, first + count); BVH_EMPTY: no child
+  int32_t _pad[4];
+};
+static_assert(sizeof(BvhNode4) == 128, "record layout");
+
 // the nearest bvh_real at or below / at or above x
 #if defined(__CUDACC__)
 __host__ __device__
@@ -97,9 +115,28 @@ struct LeafRec {     // 96 bytes: one BVH prim (any bounded leaf shape), in BVH 
   int32_t aux, _pad;     // rtc_node.aux (cylinder: index into limits)
 };
 
-// largest |coordinate| per axis of the tree: the root's first child spans it
+#if RTK_BVH_WIDE
+typedef BvhNode4 TravNode;
+#else
+typedef BvhNode TravNode;
+#endif
+
+// largest |coordinate| per axis over the children of the root = over the whole tree (inf for an all-covering box)
 inline void bvh_extent(const BvhNode& root, double ext[3]) {
-  for (int a = 0; a < 3; a++) ext[a] = std::fmax(std::fabs((double)root.lo0[a]), std::fabs((double)root.hi0[a]));
+  for (int a = 0; a < 3; a++) {
+    ext[a] = 0.0;
+    if (root.n0 >= 0) ext[a] = std::fmax(ext[a], std::fmax(std::fabs((double)root.lo0[a]), std::fabs((double)root.hi0[a])));
+    if (root.n1 >= 0) ext[a] = std::fmax(ext[a], std::fmax(std::fabs((double)root.lo1[a]), std::fabs((double)root.hi1[a])));
+  }
+}
+inline void bvh_extent(const BvhNode4& root, double ext[3]) {
+  const float* lo[3] = {root.lox, root.loy, root.loz};
+  const float* hi[3] = {root.hix, root.hiy, root.hiz};
+  for (int a = 0; a < 3; a++) {
+    ext[a] = 0.0;
+    for (int k = 0; k < 4; k++)
+      if (root.ref[k] != BVH_EMPTY) ext[a] = std::fmax(ext[a], std::fmax(std::fabs((double)lo[a][k]), std::fabs((double)hi[a][k])));
+  }
 }
 
 static_assert(sizeof(PrimRec) == 128 && sizeof(LeafRec) == 96 && sizeof(BvhNode) == (RTK_BVH_F32 ? 64 : 128), "record layout");
@@ -137,8 +174,17 @@ struct AccelBuild {
   std::vector<int32_t> prims;      // node indices: [0, n_always) tested for every ray (ascending), then BVH leaf order
   int32_t n_always = 0;
   int32_t n_sph = 0, n_pl = 0;     // the always-prefix is ordered spheres, planes, everything else
-  std::vector<BvhNode> bvh;        // node 0 = root (empty vector: no BVH)
+  std::vector<BvhNode> bvh;        // the binary tree; node 0 = root holder (empty vector: no BVH)
+  std::vector<BvhNode4> wide;      // RTK_BVH_WIDE: `bvh` collapsed to four children per node (collapse_wide), node 0 = root
   int32_t max_depth = 0;
+  int32_t wide_stack_need = 0;
+#if RTK_BVH_WIDE
+  const TravNode* trav_data() const { return wide.data(); }
+  size_t trav_count() const { return wide.size(); }
+#else
+  const TravNode* trav_data() const { return bvh.data(); }
+  size_t trav_count() const { return bvh.size(); }
+#endif
   SphCull sph_cull[SPH_CULL_MAX];
   CubeDir cube_dirs[CUBE_DIR_MAX] = {};
   int32_t n_cube_dirs = 0;
@@ -262,8 +308,85 @@ struct Prim {
 };
 
 constexpr int SAH_BINS = 16;
-constexpr double SAH_KT = 2.0;         // cost of visiting one node, in leaf tests
+constexpr int LEAF_TRI = 3;            // triangles / spheres per leaf
 constexpr double SAH_W_GENERIC = 3.0;  // cost of a generic leaf test (cube / cylinder / cone), in triangle tests
+
+// The binary tree `b2` (node 0: holder whose first child is the whole tree) as four-child nodes. A wide node starts as
+// the two children of a binary node; while it has room, its inner child with the largest surface area is replaced by
+// that child's own two children. `max_children` = 2 keeps the binary shape (one wide node per binary node).
+// Returns the traversal stack the tree can need: along any root-to-leaf path, every node leaves at most (children - 1)
+// siblings on the stack.
+inline int collapse_wide(const std::vector<BvhNode>& b2, std::vector<BvhNode4>& out, int max_children) {
+  struct Ch { float lo[3], hi[3]; int32_t c, n; };
+  auto child = [](const BvhNode& nd, int which) {
+    Ch c;
+    for (int a = 0; a < 3; a++) { c.lo[a] = which ? nd.lo1[a] : nd.lo0[a]; c.hi[a] = which ? nd.hi1[a] : nd.hi0[a]; }
+    c.c = which ? nd.c1 : nd.c0;
+    c.n = which ? nd.n1 : nd.n0;
+    return c;
+  };
+  auto empty4 = [] {
+    BvhNode4 w;
+    for (int k = 0; k < 4; k++) {
+      w.lox[k] = w.loy[k] = w.loz[k] = HUGE_VALF;
+      w.hix[k] = w.hiy[k] = w.hiz[k] = -HUGE_VALF;
+      w.ref[k] = BVH_EMPTY;
+      w._pad[k] = 0;
+    }
+    return w;
+  };
+  out.clear();
+  if (b2.empty()) return 0;
+  struct Todo { int32_t src, dst, above; };  // binary node, wide node, stack entries the path to it can hold
+  std::vector<Todo> todo;
+  out.push_back(empty4());
+  todo.push_back({0, 0, 0});
+  int need = 0;
+  while (!todo.empty()) {
+    const Todo t = todo.back();
+    todo.pop_back();
+    Ch list[4];
+    int m = 0;
+    for (int which = 0; which < 2; which++)
+      if ((which ? b2[(size_t)t.src].n1 : b2[(size_t)t.src].n0) >= 0) list[m++] = child(b2[(size_t)t.src], which);
+    // (a holder's single inner child is always opened: a one-child node would only cost a fetch)
+    while (m < max_children || m == 1) {
+      int best = -1;
+      double ba = -1.0;
+      for (int k = 0; k < m; k++) {
+        if (list[k].n != 0) continue;
+        const double dx = (double)list[k].hi[0] - list[k].lo[0], dy = (double)list[k].hi[1] - list[k].lo[1], dz = (double)list[k].hi[2] - list[k].lo[2];
+        const double area = dx * dy + dy * dz + dz * dx;
+        if (best < 0 || area > ba) { best = k; ba = area; }
+      }
+      if (best < 0) break;
+      const BvhNode& nd = b2[(size_t)list[best].c];
+      const Ch a = child(nd, 0), b = child(nd, 1);
+      const bool ha = a.n >= 0, hb = b.n >= 0;
+      if (ha && hb) { list[best] = a; list[m++] = b; }
+      else if (ha || hb) list[best] = ha ? a : b;
+      else { list[best] = list[m - 1]; m--; }
+      if (m == 0) break;
+    }
+    BvhNode4 w = empty4();
+    const int below = t.above + (m > 0 ? m - 1 : 0);
+    need = std::max(need, below);
+    for (int k = 0; k < m; k++) {
+      w.lox[k] = list[k].lo[0]; w.loy[k] = list[k].lo[1]; w.loz[k] = list[k].lo[2];
+      w.hix[k] = list[k].hi[0]; w.hiy[k] = list[k].hi[1]; w.hiz[k] = list[k].hi[2];
+      if (list[k].n > 0) {
+        w.ref[k] = ~((list[k].c << 3) | list[k].n);
+      } else {
+        const int32_t id = (int32_t)out.size();
+        out.push_back(empty4());
+        w.ref[k] = id;
+        todo.push_back({list[k].c, id, below});
+      }
+    }
+    out[(size_t)t.dst] = w;
+  }
+  return need;
+}
 
 struct Builder {
   std::vector<Prim>& prims;
@@ -381,20 +504,24 @@ struct Builder {
         if (cost < best_cost) { best_cost = cost; best_axis = a; best_bin = k; }
       }
     }
-    // The SAH's own stop. A leaf of n prims costs sum(w) leaf tests whenever its box is entered; splitting costs one more
-    // node visit (SAH_KT leaf tests' worth: a 64-byte node and two single-precision slab tests against a 96-byte record
-    // and a double-precision Moeller-Trumbore or quadratic) plus the children's expected tests. w = 1 for triangles
-    // and spheres, SAH_W_GENERIC for the kinds that go through the generic leaf test (cube, cylinder, cone).
+    // When to stop (profiles/r02ag_leafmax.log, r02ah_sah_stop.log: leaf sizes 1-6 and a cost-based stop on the three BVH
+    // workloads): up to LEAF_TRI triangles / spheres make a leaf — their tests are cheap next to the node visits a
+    // further split adds — while the kinds that go through the generic leaf test (cube, cylinder, cone) get a leaf each
+    // (cover.yml: 3.47 -> 2.88 ms). RTC_SAH_KT=<cost of a node visit in leaf tests> switches to the SAH's own stop rule
+    // instead (experiments; it wins on the million-triangle mesh and loses a third on the teapot).
     if (leaf_max == 0 && n <= 7) {
-      static const double kt = [] { const char* e = std::getenv("RTC_SAH_KT"); return e ? std::atof(e) : SAH_KT; }();
-      static const double wg = [] { const char* e = std::getenv("RTC_SAH_WG"); return e ? std::atof(e) : SAH_W_GENERIC; }();
-      double wsum = 0.0;
+      static const double kt = [] { const char* e = std::getenv("RTC_SAH_KT"); return e ? std::atof(e) : -1.0; }();
+      int n_generic = 0;
       for (int k = b; k < e; k++) {
         const int32_t kind = desc->nodes[prims[(size_t)k].node].kind;
-        wsum += (kind == RTC_TRIANGLE || kind == RTC_SMOOTH_TRIANGLE || kind == RTC_SPHERE) ? 1.0 : wg;
+        n_generic += (kind == RTC_TRIANGLE || kind == RTC_SMOOTH_TRIANGLE || kind == RTC_SPHERE) ? 0 : 1;
       }
-      const double area = bounds.area();
-      if (best_axis < 0 || !(kt * area + best_cost * (wsum / n) < wsum * area)) return -1;
+      if (kt < 0.0) {
+        if (n_generic == 0 && n <= LEAF_TRI) return -1;
+      } else {
+        const double wsum = (n - n_generic) + SAH_W_GENERIC * n_generic, area = bounds.area();
+        if (best_axis < 0 || !(kt * area + best_cost * (wsum / n) < wsum * area)) return -1;
+      }
     }
     int mid;
     if (best_axis < 0) {  // all centroids coincide: split in the middle
@@ -540,6 +667,16 @@ struct Builder {
       if (nd.n0 > 0) nd.c0 += shift;
       if (nd.n1 > 0) nd.c1 += shift;
     }
+#if RTK_BVH_WIDE
+    {
+      static const int width = [] { const char* e = std::getenv("RTC_BVH_WIDTH"); int v = e ? std::atoi(e) : 4; return v < 2 ? 2 : (v > 4 ? 4 : v); }();
+      int need = collapse_wide(out.bvh, out.wide, width);
+      // the traversal stack is WIDE_STACK_MAX entries (rt_accel.cuh: BVH_STACK): a tree that could need more keeps its
+      // binary shape, whose need is its depth (bounded by the builder)
+      if (need + 2 > WIDE_STACK_MAX) need = collapse_wide(out.bvh, out.wide, 2);
+      out.wide_stack_need = need;
+    }
+#endif
     for (int k = 0; k < n; k++) out.prims.push_back(prims[(size_t)k].node);
     out.leaf_recs.assign((size_t)n, LeafRec{});
     for (int k = 0; k < n; k++) {

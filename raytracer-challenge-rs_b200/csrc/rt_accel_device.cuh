@@ -179,7 +179,7 @@ struct Box3 {
 // ever moved), but WHERE the run is cut is chosen by the surface-area heuristic: the run is cut into 32 equal-count
 // chunks (one per lane), prefix and suffix boxes come from two warp scans, and the cheapest of the 31 cuts wins.
 __global__ void sah_level_kernel(const Range* __restrict__ in, int n_in, Range* __restrict__ out, int* __restrict__ n_out,
-                                 const double* __restrict__ cbox, int n_prims, int32_t shift, BvhNode* __restrict__ nodes,
+                                 const double* __restrict__ cbox, int n_prims, int32_t shift, TravNode* __restrict__ nodes,
                                  int* __restrict__ n_nodes, int* __restrict__ max_depth) {
   const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (w >= n_in) return;
@@ -222,6 +222,30 @@ __global__ void sah_level_kernel(const Range* __restrict__ in, int n_in, Range* 
   if (lane == 0) {
     const int nl = cut - r.first, nr = r.count - nl;
     auto leaf_count = [&](int c) { const int first = c * LEAF_PRIMS; return n_prims - first < LEAF_PRIMS ? n_prims - first : LEAF_PRIMS; };
+    int n_new = (nl > 1 ? 1 : 0) + (nr > 1 ? 1 : 0);
+    int id = n_new ? atomicAdd(n_nodes, n_new) : 0;
+    int slot = n_new ? atomicAdd(n_out, n_new) : 0;
+    int32_t c0, n0, c1, n1;
+    if (nl == 1) { c0 = shift + r.first * LEAF_PRIMS; n0 = leaf_count(r.first); }
+    else { c0 = id; n0 = 0; out[slot++] = Range{r.first, nl, id, r.depth + 1}; id++; }
+    if (nr == 1) { c1 = shift + cut * LEAF_PRIMS; n1 = leaf_count(cut); }
+    else { c1 = id; n1 = 0; out[slot] = Range{cut, nr, id, r.depth + 1}; }
+#if RTK_BVH_WIDE
+    // (the device tree keeps its binary shape: two of the four child slots)
+    BvhNode4 nd;
+    for (int k = 0; k < 4; k++) {
+      nd.lox[k] = nd.loy[k] = nd.loz[k] = HUGE_VALF;
+      nd.hix[k] = nd.hiy[k] = nd.hiz[k] = -HUGE_VALF;
+      nd.ref[k] = BVH_EMPTY;
+      nd._pad[k] = 0;
+    }
+    nd.lox[0] = bvh_below(lbox.lo[0]); nd.loy[0] = bvh_below(lbox.lo[1]); nd.loz[0] = bvh_below(lbox.lo[2]);
+    nd.hix[0] = bvh_above(lbox.hi[0]); nd.hiy[0] = bvh_above(lbox.hi[1]); nd.hiz[0] = bvh_above(lbox.hi[2]);
+    nd.lox[1] = bvh_below(rbox.lo[0]); nd.loy[1] = bvh_below(rbox.lo[1]); nd.loz[1] = bvh_below(rbox.lo[2]);
+    nd.hix[1] = bvh_above(rbox.hi[0]); nd.hiy[1] = bvh_above(rbox.hi[1]); nd.hiz[1] = bvh_above(rbox.hi[2]);
+    nd.ref[0] = n0 > 0 ? ~((c0 << 3) | n0) : c0;
+    nd.ref[1] = n1 > 0 ? ~((c1 << 3) | n1) : c1;
+#else
     BvhNode nd;
     for (int a = 0; a < 3; a++) {
       nd.lo0[a] = bvh_below(lbox.lo[a]); nd.hi0[a] = bvh_above(lbox.hi[a]);
@@ -230,13 +254,8 @@ __global__ void sah_level_kernel(const Range* __restrict__ in, int n_in, Range* 
 #if !RTK_BVH_F32
     nd._pad[0] = nd._pad[1] = nd._pad[2] = nd._pad[3] = 0;
 #endif
-    int n_new = (nl > 1 ? 1 : 0) + (nr > 1 ? 1 : 0);
-    int id = n_new ? atomicAdd(n_nodes, n_new) : 0;
-    int slot = n_new ? atomicAdd(n_out, n_new) : 0;
-    if (nl == 1) { nd.c0 = shift + r.first * LEAF_PRIMS; nd.n0 = leaf_count(r.first); }
-    else { nd.c0 = id; nd.n0 = 0; out[slot++] = Range{r.first, nl, id, r.depth + 1}; id++; }
-    if (nr == 1) { nd.c1 = shift + cut * LEAF_PRIMS; nd.n1 = leaf_count(cut); }
-    else { nd.c1 = id; nd.n1 = 0; out[slot] = Range{cut, nr, id, r.depth + 1}; }
+    nd.c0 = c0; nd.n0 = n0; nd.c1 = c1; nd.n1 = n1;
+#endif
     nodes[r.node] = nd;
     atomicMax(max_depth, r.depth + 1);
   }
@@ -264,7 +283,7 @@ inline size_t node_count(int n_prims) {
 
 // Builds nodes[node_count(n)] and recs[n] (device memory) on `stream`. Returns cudaSuccess and *ok = false when the
 // host builder has to take over (non-finite box, tree deeper than the traversal stack).
-inline cudaError_t build(const In& in, int32_t shift, BvhNode* nodes, LeafRec* recs, cudaStream_t stream, bool* ok, int* depth_out) {
+inline cudaError_t build(const In& in, int32_t shift, TravNode* nodes, LeafRec* recs, cudaStream_t stream, bool* ok, int* depth_out) {
   *ok = false;
   const int n = in.n, nc = (n + LEAF_PRIMS - 1) / LEAF_PRIMS;
   auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
@@ -314,12 +333,23 @@ inline cudaError_t build(const In& in, int32_t shift, BvhNode* nodes, LeafRec* r
   } else {
     // a single leaf: the root's first child holds it, the second is empty (n1 < 0); its box is never culled wrongly
     // by an all-covering extent
+#if RTK_BVH_WIDE
+    BvhNode4 root;
+    for (int k = 0; k < 4; k++) {
+      root.lox[k] = root.loy[k] = root.loz[k] = k == 0 ? -HUGE_VALF : HUGE_VALF;
+      root.hix[k] = root.hiy[k] = root.hiz[k] = k == 0 ? HUGE_VALF : -HUGE_VALF;
+      root.ref[k] = BVH_EMPTY;
+      root._pad[k] = 0;
+    }
+    root.ref[0] = ~((shift << 3) | n);
+#else
     BvhNode root;
     for (int a = 0; a < 3; a++) {
       root.lo0[a] = bvh_below(-1.7976931348623157e308); root.hi0[a] = bvh_above(1.7976931348623157e308);
       root.lo1[a] = bvh_above(1.7976931348623157e308); root.hi1[a] = bvh_below(-1.7976931348623157e308);
     }
     root.c0 = shift; root.n0 = n; root.c1 = 0; root.n1 = -1;
+#endif
     DEVB_TRY(cudaMemcpyAsync(nodes, &root, sizeof root, cudaMemcpyHostToDevice, stream));
   }
   emit_kernel<<<blocks(n), T, 0, stream>>>(in, idx2, recs);

@@ -27,7 +27,7 @@ struct SceneView {
   // traversal accelerator (rt_accel_build.hpp)
   const int32_t* parent;     // per node: innermost enclosing reference Group (outside CSGs), or -1
   const int32_t* prims;      // node indices: [0, n_always) tested for every ray, then BVH leaf order
-  const BvhNode* bvh;        // binary BVH, node 0 = root
+  const TravNode* bvh;       // the BVH the kernels traverse (four children per node), node 0 = root
   const PrimRec* recs;       // one record per always-prim
   const LeafRec* leaf_recs;  // one record per BVH prim (prims[n_always + k])
   int32_t n_nodes;

@@ -692,7 +692,7 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
     build_accel(d, accel, g_host_build_only ? 0 : device_min);
   }
   const size_t n_dev = accel.deferred ? accel.cand.size() : 0;
-  const size_t n_bvh_nodes = accel.deferred ? devbuild::node_count((int)n_dev) : accel.bvh.size();
+  const size_t n_bvh_nodes = accel.deferred ? devbuild::node_count((int)n_dev) : accel.trav_count();
   const size_t n_leaf_recs = accel.deferred ? n_dev : accel.leaf_recs.size();
   const auto t_accel = std::chrono::steady_clock::now();
   // one slab: [nodes | xforms | boxes | limits | tri_geom | tri_normals | materials | patterns | lights | csg_parent
@@ -711,7 +711,7 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
       {csg_parent.data(), sizeof(int32_t) * csg_parent.size(), 0},
       {accel.parent.data(), sizeof(int32_t) * accel.parent.size(), 0},
       {accel.prims.data(), sizeof(int32_t) * accel.prims.size(), 0},
-      {accel.deferred ? nullptr : accel.bvh.data(), sizeof(BvhNode) * n_bvh_nodes, 0},
+      {accel.deferred ? nullptr : accel.trav_data(), sizeof(TravNode) * n_bvh_nodes, 0},
       {accel.recs.data(), sizeof(PrimRec) * accel.recs.size(), 0},
       {accel.deferred ? nullptr : accel.leaf_recs.data(), sizeof(LeafRec) * n_leaf_recs, 0}};
   size_t total = 0;
@@ -728,7 +728,7 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   for (uint32_t m = 0; m < d->n_materials; m++)
     if (d->materials[m].reflective != 0.0 && d->materials[m].transparency != 0.0) s->has_branching = true;
   // 126 MB of L2 on B200: past ~64 MB of nodes + leaf records, traversal is DRAM-latency bound
-  s->big_accel = sizeof(BvhNode) * n_bvh_nodes + sizeof(LeafRec) * n_leaf_recs > ((size_t)64 << 20);
+  s->big_accel = sizeof(TravNode) * n_bvh_nodes + sizeof(LeafRec) * n_leaf_recs > ((size_t)64 << 20);
   if (const char* env = std::getenv("RTC_BIG_ACCEL")) s->big_accel = env[0] == '1';  // experiments: force the 32-warp kernels on/off
   s->slab_bytes = total;
   auto bail = [&](cudaError_t e, const char* what) {
@@ -799,7 +799,7 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
     e = cudaMemcpyAsync(tmp, accel.cand.data(), sizeof(int32_t) * n_dev, cudaMemcpyHostToDevice, s->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(tmp + cand_bytes, accel.fwd.data(), sizeof(double) * accel.fwd.size(), cudaMemcpyHostToDevice, s->stream);
     if (e == cudaSuccess)
-      e = devbuild::build(in, accel.n_always, (BvhNode*)(s->slab + parts[12].off), (LeafRec*)(s->slab + parts[14].off), s->stream, &ok, &depth);
+      e = devbuild::build(in, accel.n_always, (TravNode*)(s->slab + parts[12].off), (LeafRec*)(s->slab + parts[14].off), s->stream, &ok, &depth);
     cudaFreeAsync(tmp, s->stream);
     if (e != cudaSuccess) return bail(e, "device BVH build");
     if (std::getenv("RTC_TIMING"))
@@ -835,7 +835,7 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   v.csg_parent = (const int32_t*)(s->slab + parts[9].off);
   v.parent = (const int32_t*)(s->slab + parts[10].off);
   v.prims = (const int32_t*)(s->slab + parts[11].off);
-  v.bvh = (const BvhNode*)(s->slab + parts[12].off);
+  v.bvh = (const TravNode*)(s->slab + parts[12].off);
   v.recs = (const PrimRec*)(s->slab + parts[13].off);
   v.leaf_recs = (const LeafRec*)(s->slab + parts[14].off);
   v.n_always = accel.n_always;
@@ -846,15 +846,15 @@ int rtc_scene_create(const rtc_scene_desc* d, int device, rtc_scene** out) {
   v.n_cube_dirs = accel.n_cube_dirs;
   v.bvh_ext[0] = v.bvh_ext[1] = v.bvh_ext[2] = 0.0;
   if (n_bvh_nodes > 0) {
-    BvhNode root;
     if (accel.deferred) {  // built on the device: fetch the root (the build has completed on s->stream)
+      TravNode root;
       cudaError_t e = cudaMemcpyAsync(&root, s->slab + parts[12].off, sizeof root, cudaMemcpyDeviceToHost, s->stream);
       if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
       if (e != cudaSuccess) return bail(e, "device BVH root");
+      bvh_extent(root, v.bvh_ext);
     } else {
-      root = accel.bvh[0];
+      bvh_extent(accel.bvh[0], v.bvh_ext);
     }
-    bvh_extent(root, v.bvh_ext);
   }
   v.n_bvh = (int32_t)n_bvh_nodes;
   v.n_nodes = (int32_t)d->n_nodes;

@@ -41,7 +41,7 @@ void build_view(const rtc_scene_desc* d, Built& b) {
     if (!(d->materials[m].refractive_index > 0.0) || !std::isfinite(d->materials[m].refractive_index)) v.sane_indices = 0;
   build_accel(d, b.accel);
   v.parent = b.accel.parent.data(); v.prims = b.accel.prims.data(); v.recs = b.accel.recs.data(); v.leaf_recs = b.accel.leaf_recs.data();
-  v.bvh = b.accel.bvh.data(); v.n_always = b.accel.n_always; v.n_sph = b.accel.n_sph; v.n_pl = b.accel.n_pl; v.n_bvh = (int32_t)b.accel.bvh.size();
+  v.bvh = b.accel.trav_data(); v.n_always = b.accel.n_always; v.n_sph = b.accel.n_sph; v.n_pl = b.accel.n_pl; v.n_bvh = (int32_t)b.accel.trav_count();
   for (int k = 0; k < SPH_CULL_MAX; k++) v.sph_cull[k] = b.accel.sph_cull[k];
   for (int k = 0; k < CUBE_DIR_MAX; k++) v.cube_dirs[k] = b.accel.cube_dirs[k];
   v.n_cube_dirs = b.accel.n_cube_dirs;
