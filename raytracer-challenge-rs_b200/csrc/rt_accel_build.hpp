@@ -416,12 +416,66 @@ struct Builder {
     for (auto& t : pool) t.join();
   }
 
+  // split() for at most eight prims, which is most of the calls: every cut of the centroid order on every axis, exactly
+  // (sixteen bins over so few prims nearly always separate them all, so this is the binned answer without zeroing and
+  // scanning 48 bins), on this frame's stack. Also where the tree stops.
+  int split_small(int b, int e, const Box& bounds, int leaf_max) {
+    const int n = e - b;
+    int n_generic = 0;
+    for (int k = b; k < e; k++) {
+      const int32_t kind = desc->nodes[prims[(size_t)k].node].kind;
+      n_generic += (kind == RTC_TRIANGLE || kind == RTC_SMOOTH_TRIANGLE || kind == RTC_SPHERE) ? 0 : 1;
+    }
+    // When to stop (profiles/r02ag_leafmax.log, r02ah_sah_stop.log: leaf sizes 1-6 and a cost-based stop on the three BVH
+    // workloads): up to LEAF_TRI triangles / spheres make a leaf — their tests are cheap next to the node visits a
+    // further split adds — while the kinds that go through the generic leaf test (cube, cylinder, cone) get a leaf each
+    // (cover.yml: 3.47 -> 2.88 ms). RTC_SAH_KT=<cost of a node visit in leaf tests> switches to the SAH's own stop rule
+    // instead (experiments; it wins on the million-triangle mesh and loses a third on the teapot).
+    static const double kt = [] { const char* e = std::getenv("RTC_SAH_KT"); return e ? std::atof(e) : -1.0; }();
+    if (leaf_max == 0 && n <= 7 && kt < 0.0 && n_generic == 0 && n <= LEAF_TRI) return -1;
+    int best_axis = -1, best_pos = -1;
+    double best_cost = std::numeric_limits<double>::infinity();
+    int order[3][8];
+    for (int a = 0; a < 3; a++) {
+      int* idx = order[a];
+      for (int k = 0; k < n; k++) {  // insertion sort by centroid, stable
+        int j = k;
+        while (j > 0 && prims[(size_t)(b + idx[j - 1])].c[a] > prims[(size_t)(b + k)].c[a]) { idx[j] = idx[j - 1]; j--; }
+        idx[j] = k;
+      }
+      if (!(prims[(size_t)(b + idx[n - 1])].c[a] > prims[(size_t)(b + idx[0])].c[a])) continue;  // no extent on this axis
+      double right_area[8];
+      Box acc;
+      acc.reset();
+      for (int k = n - 1; k > 0; k--) {
+        acc.add(prims[(size_t)(b + idx[k])].box);
+        right_area[k] = acc.area();
+      }
+      acc.reset();
+      for (int k = 0; k + 1 < n; k++) {
+        acc.add(prims[(size_t)(b + idx[k])].box);
+        const double cost = acc.area() * (k + 1) + right_area[k + 1] * (n - k - 1);
+        if (cost < best_cost) { best_cost = cost; best_axis = a; best_pos = k + 1; }
+      }
+    }
+    if (leaf_max == 0 && n <= 7 && kt >= 0.0) {
+      const double wsum = (n - n_generic) + SAH_W_GENERIC * n_generic, area = bounds.area();
+      if (best_axis < 0 || !(kt * area + best_cost * (wsum / n) < wsum * area)) return -1;
+    }
+    if (best_axis < 0) return b + n / 2;  // all centroids coincide
+    Prim tmp[8];
+    for (int k = 0; k < n; k++) tmp[k] = prims[(size_t)(b + order[best_axis][k])];
+    for (int k = 0; k < n; k++) prims[(size_t)(b + k)] = tmp[k];
+    return b + best_pos;
+  }
+
   // Split prims[b,e) — returns mid (b < mid < e), or -1 to make a leaf.
   int split(int b, int e, const Box& bounds, int depth, int nthreads) {
     const int n = e - b;
     if (n <= 1) return -1;
     static const int leaf_max = [] { const char* e = std::getenv("RTC_LEAF_MAX"); int v = e ? std::atoi(e) : 0; return v < 0 ? 0 : (v > 7 ? 7 : v); }();
     if (leaf_max > 0 && n <= leaf_max) return -1;  // experiments: a fixed leaf size instead of the SAH's own stop
+    if (n <= 8) return split_small(b, e, bounds, leaf_max);
     if (depth >= 40) {  // bound the traversal stack: median split along the widest axis from here on
       int a = 0;
       for (int k = 1; k < 3; k++)
@@ -433,16 +487,21 @@ struct Builder {
     // centroid bounds, then ONE pass that bins all three axes; both passes are cut into chunks run on
     // worker threads when the range is large (the top levels of a million-triangle mesh)
     const int nchunk = (n >= PAR_MIN && nthreads > 1) ? nthreads : 1;
-    std::vector<Box> cbs((size_t)nchunk);
-    parallel_chunks(b, e, nchunk, [&](int ci, int cb0, int ce0) {
-      Box x;
-      x.reset();
-      for (int k = cb0; k < ce0; k++) x.add(prims[(size_t)k].c);
-      cbs[(size_t)ci] = x;
-    });
+    // (single-chunk ranges — all the small ones, i.e. most calls — keep their scratch on this frame: no heap traffic)
     Box cb;
     cb.reset();
-    for (const Box& x : cbs) cb.add(x);
+    if (nchunk == 1) {
+      for (int k = b; k < e; k++) cb.add(prims[(size_t)k].c);
+    } else {
+      std::vector<Box> cbs((size_t)nchunk);
+      parallel_chunks(b, e, nchunk, [&](int ci, int cb0, int ce0) {
+        Box x;
+        x.reset();
+        for (int k = cb0; k < ce0; k++) x.add(prims[(size_t)k].c);
+        cbs[(size_t)ci] = x;
+      });
+      for (const Box& x : cbs) cb.add(x);
+    }
     struct Bins {
       Box bb[3][SAH_BINS];
       int cnt[3][SAH_BINS];
@@ -454,7 +513,10 @@ struct Builder {
       use_axis[a] = ext > 0.0;
       scale3[a] = use_axis[a] ? SAH_BINS / ext : 0.0;
     }
-    std::vector<Bins> part((size_t)nchunk);
+    Bins part_local;
+    std::vector<Bins> part_heap;
+    if (nchunk > 1) part_heap.resize((size_t)nchunk);
+    Bins* part = nchunk > 1 ? part_heap.data() : &part_local;
     parallel_chunks(b, e, nchunk, [&](int ci, int cb0, int ce0) {
       Bins& B = part[(size_t)ci];
       for (int a = 0; a < 3; a++)
@@ -502,25 +564,6 @@ struct Builder {
         if (c == 0 || right_cnt[k + 1] == 0) continue;
         double cost = acc.area() * c + right_area[k + 1] * right_cnt[k + 1];
         if (cost < best_cost) { best_cost = cost; best_axis = a; best_bin = k; }
-      }
-    }
-    // When to stop (profiles/r02ag_leafmax.log, r02ah_sah_stop.log: leaf sizes 1-6 and a cost-based stop on the three BVH
-    // workloads): up to LEAF_TRI triangles / spheres make a leaf — their tests are cheap next to the node visits a
-    // further split adds — while the kinds that go through the generic leaf test (cube, cylinder, cone) get a leaf each
-    // (cover.yml: 3.47 -> 2.88 ms). RTC_SAH_KT=<cost of a node visit in leaf tests> switches to the SAH's own stop rule
-    // instead (experiments; it wins on the million-triangle mesh and loses a third on the teapot).
-    if (leaf_max == 0 && n <= 7) {
-      static const double kt = [] { const char* e = std::getenv("RTC_SAH_KT"); return e ? std::atof(e) : -1.0; }();
-      int n_generic = 0;
-      for (int k = b; k < e; k++) {
-        const int32_t kind = desc->nodes[prims[(size_t)k].node].kind;
-        n_generic += (kind == RTC_TRIANGLE || kind == RTC_SMOOTH_TRIANGLE || kind == RTC_SPHERE) ? 0 : 1;
-      }
-      if (kt < 0.0) {
-        if (n_generic == 0 && n <= LEAF_TRI) return -1;
-      } else {
-        const double wsum = (n - n_generic) + SAH_W_GENERIC * n_generic, area = bounds.area();
-        if (best_axis < 0 || !(kt * area + best_cost * (wsum / n) < wsum * area)) return -1;
       }
     }
     int mid;

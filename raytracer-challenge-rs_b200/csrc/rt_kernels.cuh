@@ -10,6 +10,10 @@
 #ifndef RTK_MIN_BLOCKS
 #define RTK_MIN_BLOCKS 4
 #endif
+// resident CTAs per SM of the kernels launched for accelerators far beyond L2 (rtc_scene::big_accel)
+#ifndef RTK_BIG_MINB
+#define RTK_BIG_MINB 8
+#endif
 
 namespace rtk {
 

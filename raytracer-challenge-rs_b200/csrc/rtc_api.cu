@@ -295,16 +295,16 @@ int launch_rows(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool fa
   if (grid.x > 0 && grid.y > 0) {
     if (s->has_csg) {
       if (faithful) render_kernel<true, true><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
-      else if (s->big_accel) render_kernel<true, false, 8><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
+      else if (s->big_accel) render_kernel<true, false, RTK_BIG_MINB><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
       else render_kernel<true, false><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
     } else if (s->lean && !faithful) {
       render_kernel<false, 2><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
     } else if (s->tri_sph_only && !faithful) {
-      if (s->big_accel) render_kernel<false, 4, 8><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
+      if (s->big_accel) render_kernel<false, 4, RTK_BIG_MINB><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
       else render_kernel<false, 4><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
     } else {
       if (faithful) render_kernel<false, true><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
-      else if (s->big_accel) render_kernel<false, false, 8><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
+      else if (s->big_accel) render_kernel<false, false, RTK_BIG_MINB><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
       else render_kernel<false, false><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
     }
     s->launches++;
@@ -421,15 +421,15 @@ int launch_wave(rtc_scene* s, const CameraD& cam, const RenderParams& P, double*
     A.level = L;
     A.work = work + L;
     if (s->has_csg) {
-      if (s->big_accel) launch_wave_level<true, 8>(s, cam, P, A, L == 0, out, stream);
+      if (s->big_accel) launch_wave_level<true, RTK_BIG_MINB>(s, cam, P, A, L == 0, out, stream);
       else launch_wave_level<true, RTK_MIN_BLOCKS>(s, cam, P, A, L == 0, out, stream);
     } else if (s->lean) {
       launch_wave_level<false, RTK_MIN_BLOCKS, 2>(s, cam, P, A, L == 0, out, stream);
     } else if (s->tri_sph_only) {
-      if (s->big_accel) launch_wave_level<false, 8, 4>(s, cam, P, A, L == 0, out, stream);
+      if (s->big_accel) launch_wave_level<false, RTK_BIG_MINB, 4>(s, cam, P, A, L == 0, out, stream);
       else launch_wave_level<false, RTK_MIN_BLOCKS, 4>(s, cam, P, A, L == 0, out, stream);
     } else {
-      if (s->big_accel) launch_wave_level<false, 8>(s, cam, P, A, L == 0, out, stream);
+      if (s->big_accel) launch_wave_level<false, RTK_BIG_MINB>(s, cam, P, A, L == 0, out, stream);
       else launch_wave_level<false, RTK_MIN_BLOCKS>(s, cam, P, A, L == 0, out, stream);
     }
   }
@@ -493,18 +493,18 @@ int launch_stream(rtc_scene* s, const CameraD& cam, const RenderParams& P, doubl
 #if defined(RTK_STREAM_STATS)
   CUDA_TRY(cudaMemsetAsync(s->d_counters + 8, 0, 16 * sizeof(unsigned long long), stream));
 #endif
-  const int minb = s->big_accel ? 8 : RTK_MIN_BLOCKS;
+  const int minb = s->big_accel ? RTK_BIG_MINB : RTK_MIN_BLOCKS;
   const int grid = s->sm_count * minb;
   if (s->has_csg) {
-    if (s->big_accel) wave_stream_kernel<true, 8><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+    if (s->big_accel) wave_stream_kernel<true, RTK_BIG_MINB><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
     else wave_stream_kernel<true, RTK_MIN_BLOCKS><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
   } else if (s->lean) {
     wave_stream_kernel<false, RTK_MIN_BLOCKS, 2><<<s->sm_count * RTK_MIN_BLOCKS, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
   } else if (s->tri_sph_only) {
-    if (s->big_accel) wave_stream_kernel<false, 8, 4><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+    if (s->big_accel) wave_stream_kernel<false, RTK_BIG_MINB, 4><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
     else wave_stream_kernel<false, RTK_MIN_BLOCKS, 4><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
   } else {
-    if (s->big_accel) wave_stream_kernel<false, 8><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+    if (s->big_accel) wave_stream_kernel<false, RTK_BIG_MINB><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
     else wave_stream_kernel<false, RTK_MIN_BLOCKS><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
   }
   s->launches++;
