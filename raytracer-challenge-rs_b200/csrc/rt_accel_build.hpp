@@ -305,6 +305,7 @@ struct Prim {
   Box box;
   double c[3];
   int32_t node;
+  int32_t generic;  // 1: goes through the generic leaf test (cube, cylinder, cone); 0: triangle / sphere
 };
 
 constexpr int SAH_BINS = 16;
@@ -394,12 +395,15 @@ struct Builder {
   const rtc_scene_desc* desc;
   int threads = 1;                         // worker threads for large ranges / independent subtrees
   int PAR_MIN = 1 << 16;                   // ranges below this are binned on the calling thread
+  int PAR_SUBTREES_MIN = 8192;             // trees below this are built on the calling thread alone
+  std::vector<Prim> scratch;               // the parallel partition's other buffer
   explicit Builder(std::vector<Prim>& p, AccelBuild& o, const rtc_scene_desc* d) : prims(p), out(o), desc(d) {
     unsigned hc = std::thread::hardware_concurrency();
     threads = hc == 0 ? 1 : (hc > 16 ? 16 : (int)hc);
     if (const char* v = std::getenv("RTC_BVH_THREADS")) threads = std::max(1, std::min(64, std::atoi(v)));
     if (const char* v = std::getenv("RTC_BVH_PAR_MIN")) {  // tests: push small meshes through the threaded path
       PAR_MIN = std::max(8, std::atoi(v));
+      PAR_SUBTREES_MIN = 4 * PAR_MIN;
       if (threads < 4) threads = 4;
     }
   }
@@ -419,13 +423,10 @@ struct Builder {
   // split() for at most eight prims, which is most of the calls: every cut of the centroid order on every axis, exactly
   // (sixteen bins over so few prims nearly always separate them all, so this is the binned answer without zeroing and
   // scanning 48 bins), on this frame's stack. Also where the tree stops.
-  int split_small(int b, int e, const Box& bounds, int leaf_max) {
+  int split_small(int b, int e, const Box& bounds, int leaf_max, Box* child_box, bool* have_boxes) {
     const int n = e - b;
     int n_generic = 0;
-    for (int k = b; k < e; k++) {
-      const int32_t kind = desc->nodes[prims[(size_t)k].node].kind;
-      n_generic += (kind == RTC_TRIANGLE || kind == RTC_SMOOTH_TRIANGLE || kind == RTC_SPHERE) ? 0 : 1;
-    }
+    for (int k = b; k < e; k++) n_generic += prims[(size_t)k].generic;
     // When to stop (profiles/r02ag_leafmax.log, r02ah_sah_stop.log: leaf sizes 1-6 and a cost-based stop on the three BVH
     // workloads): up to LEAF_TRI triangles / spheres make a leaf — their tests are cheap next to the node visits a
     // further split adds — while the kinds that go through the generic leaf test (cube, cylinder, cone) get a leaf each
@@ -465,17 +466,26 @@ struct Builder {
     if (best_axis < 0) return b + n / 2;  // all centroids coincide
     Prim tmp[8];
     for (int k = 0; k < n; k++) tmp[k] = prims[(size_t)(b + order[best_axis][k])];
-    for (int k = 0; k < n; k++) prims[(size_t)(b + k)] = tmp[k];
+    child_box[0].reset();
+    child_box[1].reset();
+    for (int k = 0; k < n; k++) {
+      prims[(size_t)(b + k)] = tmp[k];
+      child_box[k < best_pos ? 0 : 1].add(tmp[k].box);
+    }
+    *have_boxes = true;
     return b + best_pos;
   }
 
-  // Split prims[b,e) — returns mid (b < mid < e), or -1 to make a leaf.
-  int split(int b, int e, const Box& bounds, int depth, int nthreads) {
+  // Split prims[b,e) — returns mid (b < mid < e), or -1 to make a leaf. When the cut came from the bins (or the small
+  // sweep) the two sides' boxes are already known: child_box[0..1], *have_boxes (the same min/max over the same prim
+  // boxes as range_box, bit for bit), which saves the caller a pass over each child.
+  int split(int b, int e, const Box& bounds, int depth, int nthreads, Box* child_box, bool* have_boxes) {
     const int n = e - b;
+    *have_boxes = false;
     if (n <= 1) return -1;
     static const int leaf_max = [] { const char* e = std::getenv("RTC_LEAF_MAX"); int v = e ? std::atoi(e) : 0; return v < 0 ? 0 : (v > 7 ? 7 : v); }();
     if (leaf_max > 0 && n <= leaf_max) return -1;  // experiments: a fixed leaf size instead of the SAH's own stop
-    if (n <= 8) return split_small(b, e, bounds, leaf_max);
+    if (n <= 8) return split_small(b, e, bounds, leaf_max, child_box, have_boxes);
     if (depth >= 40) {  // bound the traversal stack: median split along the widest axis from here on
       int a = 0;
       for (int k = 1; k < 3; k++)
@@ -574,13 +584,57 @@ struct Builder {
       const double ext = cb.hi[best_axis] - cb.lo[best_axis];
       const double scale = SAH_BINS / ext, lo = cb.lo[best_axis];
       const int a = best_axis, bin = best_bin;
-      auto it = std::partition(prims.begin() + b, prims.begin() + e, [&](const Prim& p) {
+      auto goes_left = [&](const Prim& p) {
         int bi = (int)((p.c[a] - lo) * scale);
         bi = bi < 0 ? 0 : (bi >= SAH_BINS ? SAH_BINS - 1 : bi);
         return bi <= bin;
-      });
-      mid = (int)(it - prims.begin());
-      if (mid == b || mid == e) mid = b + n / 2;
+      };
+      if (nchunk > 1) {
+        // the top levels of a big mesh: every chunk knows from its bins how many of its prims go left, so all chunks
+        // scatter into `scratch` at once (a serial std::partition of a million 80-byte prims is ~30 ms per level)
+        std::vector<int> lc((size_t)nchunk, 0);
+        int total_left = 0;
+        for (int k = 0; k <= bin; k++) total_left += part[0].cnt[a][k];  // part[0] holds the merged counts
+        int others = 0;
+        for (int ci = 1; ci < nchunk; ci++) {
+          for (int k = 0; k <= bin; k++) lc[(size_t)ci] += part[ci].cnt[a][k];
+          others += lc[(size_t)ci];
+        }
+        lc[0] = total_left - others;
+        std::vector<int> loff((size_t)nchunk), roff((size_t)nchunk);
+        int lacc = 0, racc = total_left;
+        for (int ci = 0; ci < nchunk; ci++) {
+          const int cb0 = b + (int)((long long)n * ci / nchunk), ce0 = b + (int)((long long)n * (ci + 1) / nchunk);
+          loff[(size_t)ci] = lacc;
+          roff[(size_t)ci] = racc;
+          lacc += lc[(size_t)ci];
+          racc += (ce0 - cb0) - lc[(size_t)ci];
+        }
+        if (scratch.size() < (size_t)n) scratch.resize((size_t)n);
+        parallel_chunks(b, e, nchunk, [&](int ci, int cb0, int ce0) {
+          int l = loff[(size_t)ci], r = roff[(size_t)ci];
+          for (int k = cb0; k < ce0; k++) {
+            const Prim& p = prims[(size_t)k];
+            scratch[(size_t)(goes_left(p) ? l++ : r++)] = p;
+          }
+        });
+        parallel_chunks(b, e, nchunk, [&](int, int cb0, int ce0) {
+          std::copy(scratch.begin() + (cb0 - b), scratch.begin() + (ce0 - b), prims.begin() + cb0);
+        });
+        mid = b + total_left;
+      } else {
+        auto it = std::partition(prims.begin() + b, prims.begin() + e, goes_left);
+        mid = (int)(it - prims.begin());
+      }
+      if (mid == b || mid == e) {
+        mid = b + n / 2;
+      } else {
+        child_box[0].reset();
+        child_box[1].reset();
+        for (int k = 0; k < SAH_BINS; k++)
+          if (part[0].cnt[a][k]) child_box[k <= bin ? 0 : 1].add(part[0].bb[a][k]);
+        *have_boxes = true;
+      }
     }
     return mid;
   }
@@ -599,7 +653,7 @@ struct Builder {
     if (which) { nd.c1 = c; nd.n1 = n; } else { nd.c0 = c; nd.n0 = n; }
   }
 
-  struct Task { int b, e, node, which, depth; };
+  struct Task { int b, e, node, which, depth; bool has_box; Box box; };
 
   // Build the subtrees on `stack` into `nodes`. With `deferred`, a range of fewer than defer_below prims
   // is not built but handed back (its parent slot stays empty until the caller splices the subtree in).
@@ -616,7 +670,9 @@ struct Builder {
       }
       max_depth = std::max(max_depth, (int32_t)t.depth);
       Box bx;
-      if (t.e - t.b >= PAR_MIN && nthreads > 1) {
+      if (t.has_box) {
+        bx = t.box;
+      } else if (t.e - t.b >= PAR_MIN && nthreads > 1) {
         std::vector<Box> parts((size_t)nthreads);
         parallel_chunks(t.b, t.e, nthreads, [&](int ci, int b0, int e0) { parts[(size_t)ci] = range_box(prims, b0, e0); });
         bx.reset();
@@ -624,7 +680,9 @@ struct Builder {
       } else {
         bx = range_box(prims, t.b, t.e);
       }
-      int mid = split(t.b, t.e, bx, t.depth, nthreads);
+      Box child_box[2];
+      bool have_boxes = false;
+      int mid = split(t.b, t.e, bx, t.depth, nthreads, child_box, &have_boxes);
       if (mid < 0) {
         std::sort(prims.begin() + t.b, prims.begin() + t.e, [](const Prim& x, const Prim& y) { return x.node < y.node; });
         set_child(nodes[(size_t)t.node], t.which, bx, t.b, t.e - t.b);
@@ -635,8 +693,8 @@ struct Builder {
         set_child(nd, 1, empty, 0, -1);
         nodes.push_back(nd);
         set_child(nodes[(size_t)t.node], t.which, bx, id, 0);
-        stack.push_back({t.b, mid, id, 0, t.depth + 1});
-        stack.push_back({mid, t.e, id, 1, t.depth + 1});
+        stack.push_back({t.b, mid, id, 0, t.depth + 1, have_boxes, child_box[0]});
+        stack.push_back({mid, t.e, id, 1, t.depth + 1, have_boxes, child_box[1]});
       }
     }
   }
@@ -653,15 +711,15 @@ struct Builder {
     set_child(root, 0, empty, 0, -1);
     set_child(root, 1, empty, 0, -1);
     out.bvh.push_back(root);
-    stack.push_back({0, n, 0, 0, 1});
-    if (n < 4 * PAR_MIN || threads <= 1) {
+    stack.push_back({0, n, 0, 0, 1, false, empty});
+    if (n < PAR_SUBTREES_MIN || threads <= 1) {
       run(out.bvh, stack, 0, nullptr, out.max_depth, 1);
     } else {
       // top of the tree on this thread (its big ranges binned by all threads), every subtree below
       // n / (4·threads) prims built by a worker into its own node vector and spliced in afterwards in
       // task order, so the tree does not depend on thread timing
       std::vector<Task> deferred;
-      run(out.bvh, stack, std::max(n / (4 * threads), std::min(4096, PAR_MIN)), &deferred, out.max_depth, threads);
+      run(out.bvh, stack, std::max(n / (4 * threads), std::min(512, PAR_MIN)), &deferred, out.max_depth, threads);
       struct Sub { std::vector<BvhNode> nodes; int32_t depth = 0; };
       std::vector<Sub> subs(deferred.size());
       std::vector<size_t> order(deferred.size());
@@ -679,7 +737,7 @@ struct Builder {
           set_child(holder, 1, empty, 0, -1);
           sb.nodes.push_back(holder);
           std::vector<Task> st;
-          st.push_back({deferred[i].b, deferred[i].e, 0, 0, deferred[i].depth});
+          st.push_back({deferred[i].b, deferred[i].e, 0, 0, deferred[i].depth, deferred[i].has_box, deferred[i].box});
           run(sb.nodes, st, 0, nullptr, sb.depth, 1);
         }
       };
@@ -891,6 +949,7 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A, size_t device_mi
     } else {
       Prim p;
       p.node = i;
+      p.generic = (nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE || nd.kind == RTC_SPHERE) ? 0 : 1;
       if (defer) {
         // eligibility without the box (the GPU computes it; a non-finite one sends the whole build back here)
         bool ok = (nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE || nd.kind == RTC_SPHERE || nd.kind == RTC_CYLINDER) &&
@@ -905,14 +964,41 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A, size_t device_mi
         } else {
           A.prims.push_back(i);
         }
-      } else if (nd.kind != RTC_PLANE && leaf_world_box(d, nd, p.box, fwd_cache, cubes_ok)) {
-        for (int a = 0; a < 3; a++) p.c[a] = 0.5 * (p.box.lo[a] + p.box.hi[a]);
-        cand.push_back(p);
+      } else if (nd.kind != RTC_PLANE) {
+        cand.push_back(p);  // its box: the pass below
       } else {
         A.prims.push_back(i);
       }
       i = i + 1;
     }
+  }
+  if (!defer && !cand.empty()) {
+    // world boxes of the candidates (three transformed vertices per triangle): on all host threads for a big scene.
+    // The forward matrices are inverted up front then (the cache is filled lazily otherwise, which is not thread-safe).
+    unsigned hc = std::thread::hardware_concurrency();
+    int nthreads = hc == 0 ? 1 : (hc > 16 ? 16 : (int)hc);
+    if (const char* v = std::getenv("RTC_BVH_THREADS")) nthreads = std::max(1, std::min(64, std::atoi(v)));
+    if (cand.size() < 65536) nthreads = 1;
+    if (nthreads > 1)
+      for (uint32_t x = 0; x < d->n_xforms; x++) fwd_cache.get(d, (int32_t)x);
+    std::vector<unsigned char> boxed(cand.size(), 0);
+    Builder::parallel_chunks(0, (int)cand.size(), nthreads, [&](int, int b0, int e0) {
+      for (int k = b0; k < e0; k++) {
+        Prim& q = cand[(size_t)k];
+        if (leaf_world_box(d, d->nodes[q.node], q.box, fwd_cache, cubes_ok)) {
+          for (int a = 0; a < 3; a++) q.c[a] = 0.5 * (q.box.lo[a] + q.box.hi[a]);
+          boxed[(size_t)k] = 1;
+        }
+      }
+    });
+    size_t kept = 0;
+    bool dropped = false;
+    for (size_t k = 0; k < cand.size(); k++) {
+      if (boxed[k]) { if (kept != k) cand[kept] = cand[k]; kept++; }
+      else { A.prims.push_back(cand[k].node); dropped = true; }
+    }
+    cand.resize(kept);
+    if (dropped) std::sort(A.prims.begin(), A.prims.end());  // every-ray prims stay in node order
   }
   // Nested boxes let one test stand for a whole chain. For one ray, per-axis slab intervals are
   // monotone in the box bounds even in floating point (x - o and x / d are monotone, and the

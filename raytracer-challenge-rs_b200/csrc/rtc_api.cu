@@ -124,38 +124,38 @@ int validate(const rtc_scene_desc* d, std::vector<int32_t>& csg_parent, bool& ha
   for (int32_t i = 0; i < n; i++) {
     while (!open.empty() && open.back().end == i) open.pop_back();
     const rtc_node& nd = d->nodes[i];
-    char where[64];
-    std::snprintf(where, sizeof where, "node %d: ", i);
+    // (the message prefix is only formatted on failure: a snprintf per node was 60 ms of a million-node scene)
+    auto where = [i]() { return "node " + std::to_string(i) + ": "; };
     int32_t limit = open.empty() ? n : open.back().end;
     for (auto it = open.rbegin(); it != open.rend(); ++it)
       if (it->csg) { csg_parent[(size_t)i] = it->node; break; }
-    if (nd.kind < RTC_SPHERE || nd.kind > RTC_CSG) return fail(RTC_ERR_INVALID, std::string(where) + "bad kind");
+    if (nd.kind < RTC_SPHERE || nd.kind > RTC_CSG) return fail(RTC_ERR_INVALID, where() + "bad kind");
     bool aggregate = nd.kind == RTC_GROUP || nd.kind == RTC_CSG;
     if (!aggregate) {
-      if (nd.skip != i + 1) return fail(RTC_ERR_INVALID, std::string(where) + "leaf skip must be index+1");
-      if (nd.xform < 0 || (uint32_t)nd.xform >= d->n_xforms) return fail(RTC_ERR_INVALID, std::string(where) + "xform out of range");
-      if (nd.material < 0 || (uint32_t)nd.material >= d->n_materials) return fail(RTC_ERR_INVALID, std::string(where) + "material out of range");
+      if (nd.skip != i + 1) return fail(RTC_ERR_INVALID, where() + "leaf skip must be index+1");
+      if (nd.xform < 0 || (uint32_t)nd.xform >= d->n_xforms) return fail(RTC_ERR_INVALID, where() + "xform out of range");
+      if (nd.material < 0 || (uint32_t)nd.material >= d->n_materials) return fail(RTC_ERR_INVALID, where() + "material out of range");
       if ((nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE) && (nd.aux < 0 || (uint32_t)nd.aux >= d->n_triangles))
-        return fail(RTC_ERR_INVALID, std::string(where) + "triangle index out of range");
+        return fail(RTC_ERR_INVALID, where() + "triangle index out of range");
       if ((nd.kind == RTC_CYLINDER || nd.kind == RTC_CONE) && (nd.aux < 0 || (uint32_t)nd.aux >= d->n_limits))
-        return fail(RTC_ERR_INVALID, std::string(where) + "limits index out of range");
+        return fail(RTC_ERR_INVALID, where() + "limits index out of range");
     } else {
-      if (nd.skip <= i || nd.skip > limit) return fail(RTC_ERR_INVALID, std::string(where) + "skip out of range");
-      if (nd.aux < 0 || (uint32_t)nd.aux >= d->n_boxes) return fail(RTC_ERR_INVALID, std::string(where) + "box index out of range");
+      if (nd.skip <= i || nd.skip > limit) return fail(RTC_ERR_INVALID, where() + "skip out of range");
+      if (nd.aux < 0 || (uint32_t)nd.aux >= d->n_boxes) return fail(RTC_ERR_INVALID, where() + "box index out of range");
       if (nd.kind == RTC_CSG) {
         has_csg = true;
-        if (nd.xform < 0 || (uint32_t)nd.xform >= d->n_xforms) return fail(RTC_ERR_INVALID, std::string(where) + "xform out of range");
-        if (nd.right <= i + 1 || nd.right >= nd.skip) return fail(RTC_ERR_INVALID, std::string(where) + "CSG right index out of range");
-        if (d->nodes[i + 1].skip != nd.right) return fail(RTC_ERR_INVALID, std::string(where) + "CSG left subtree must end at right");
-        if (d->nodes[nd.right].skip != nd.skip) return fail(RTC_ERR_INVALID, std::string(where) + "CSG right subtree must end at skip");
-        if (((nd.flags >> 8) & 3u) > 2u) return fail(RTC_ERR_INVALID, std::string(where) + "bad CSG op");
+        if (nd.xform < 0 || (uint32_t)nd.xform >= d->n_xforms) return fail(RTC_ERR_INVALID, where() + "xform out of range");
+        if (nd.right <= i + 1 || nd.right >= nd.skip) return fail(RTC_ERR_INVALID, where() + "CSG right index out of range");
+        if (d->nodes[i + 1].skip != nd.right) return fail(RTC_ERR_INVALID, where() + "CSG left subtree must end at right");
+        if (d->nodes[nd.right].skip != nd.skip) return fail(RTC_ERR_INVALID, where() + "CSG right subtree must end at skip");
+        if (((nd.flags >> 8) & 3u) > 2u) return fail(RTC_ERR_INVALID, where() + "bad CSG op");
         int depth = 1;
         for (auto& o : open) depth += o.csg ? 1 : 0;
-        if (depth > CSG_MAX_DEPTH) return fail(RTC_ERR_UNSUPPORTED, std::string(where) + "CSG nesting deeper than 4");
+        if (depth > CSG_MAX_DEPTH) return fail(RTC_ERR_UNSUPPORTED, where() + "CSG nesting deeper than 4");
       }
       if (nd.skip > i + 1) open.push_back({nd.skip, nd.kind == RTC_CSG, i});
     }
-    if (nd.skip > limit) return fail(RTC_ERR_INVALID, std::string(where) + "subtree crosses its parent");
+    if (nd.skip > limit) return fail(RTC_ERR_INVALID, where() + "subtree crosses its parent");
   }
   for (uint32_t m = 0; m < d->n_materials; m++) {
     int32_t p = d->materials[m].pattern;
