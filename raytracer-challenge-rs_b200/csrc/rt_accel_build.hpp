@@ -712,6 +712,7 @@ struct Builder {
     set_child(root, 1, empty, 0, -1);
     out.bvh.push_back(root);
     stack.push_back({0, n, 0, 0, 1, false, empty});
+    const auto tb0 = std::chrono::steady_clock::now();
     if (n < PAR_SUBTREES_MIN || threads <= 1) {
       run(out.bvh, stack, 0, nullptr, out.max_depth, 1);
     } else {
@@ -719,7 +720,13 @@ struct Builder {
       // n / (4·threads) prims built by a worker into its own node vector and spliced in afterwards in
       // task order, so the tree does not depend on thread timing
       std::vector<Task> deferred;
-      run(out.bvh, stack, std::max(n / (4 * threads), std::min(512, PAR_MIN)), &deferred, out.max_depth, threads);
+      // (a big mesh hands out everything the calling thread would otherwise bin alone, i.e. below PAR_MIN: million
+      // triangles, top of the tree 100 -> 63 ms, profiles/r02av_defer.log)
+      int defer_below = std::max(n / (4 * threads), std::min(512, PAR_MIN));
+      if (n >= 4 * PAR_MIN) defer_below = std::max(defer_below, PAR_MIN);
+      if (const char* v = std::getenv("RTC_BVH_DEFER_BELOW")) defer_below = std::max(8, std::atoi(v));
+      run(out.bvh, stack, defer_below, &deferred, out.max_depth, threads);
+      const auto tp1 = std::chrono::steady_clock::now();
       struct Sub { std::vector<BvhNode> nodes; int32_t depth = 0; };
       std::vector<Sub> subs(deferred.size());
       std::vector<size_t> order(deferred.size());
@@ -745,6 +752,10 @@ struct Builder {
       for (int t = 1; t < threads; t++) pool.emplace_back(worker);
       worker();
       for (auto& t : pool) t.join();
+      if (std::getenv("RTC_TIMING"))
+        std::fprintf(stderr, "BVH build: top of the tree %.1f ms (%zu subtrees handed out), subtrees %.1f ms\n",
+                     std::chrono::duration<double, std::milli>(tp1 - tb0).count(), deferred.size(),
+                     std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tp1).count());
       for (size_t i = 0; i < deferred.size(); i++) {
         const Sub& sb = subs[i];
         const int32_t base = (int32_t)out.bvh.size() - 1;  // local node j (>= 1) becomes base + j
@@ -762,6 +773,7 @@ struct Builder {
         out.max_depth = std::max(out.max_depth, sb.depth);
       }
     }
+    const auto tb1 = std::chrono::steady_clock::now();
     // BVH leaves address the combined prim array: shift by the always-prefix
     const int32_t shift = (int32_t)out.prims.size();
     for (auto& nd : out.bvh) {
@@ -778,17 +790,29 @@ struct Builder {
       out.wide_stack_need = need;
     }
 #endif
-    for (int k = 0; k < n; k++) out.prims.push_back(prims[(size_t)k].node);
-    out.leaf_recs.assign((size_t)n, LeafRec{});
-    for (int k = 0; k < n; k++) {
-      const int32_t i = prims[(size_t)k].node;
-      const rtc_node& nd = desc->nodes[i];
-      LeafRec& r = out.leaf_recs[(size_t)k];
-      r.node = i; r.xform = nd.xform; r.parent = out.parent[(size_t)i];
-      r.kind_flags = ((uint32_t)nd.kind << 24) | (nd.flags & 0xffffffu);
-      r.aux = nd.aux;
-      if (nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE)
-        for (int c = 0; c < 9; c++) r.g[c] = desc->tri_p1e1e2[9 * (size_t)nd.aux + c];
+    // the leaf records gather from the node and triangle tables in BVH order, i.e. at random: on all threads for a
+    // big mesh (serially it was a third of the million-triangle build)
+    const size_t base = out.prims.size();
+    out.prims.resize(base + (size_t)n);
+    out.leaf_recs.resize((size_t)n);
+    parallel_chunks(0, n, n >= PAR_MIN ? threads : 1, [&](int, int k0, int k1) {
+      for (int k = k0; k < k1; k++) {
+        const int32_t i = prims[(size_t)k].node;
+        const rtc_node& nd = desc->nodes[i];
+        out.prims[base + (size_t)k] = i;
+        LeafRec r{};
+        r.node = i; r.xform = nd.xform; r.parent = out.parent[(size_t)i];
+        r.kind_flags = ((uint32_t)nd.kind << 24) | (nd.flags & 0xffffffu);
+        r.aux = nd.aux;
+        if (nd.kind == RTC_TRIANGLE || nd.kind == RTC_SMOOTH_TRIANGLE)
+          for (int c = 0; c < 9; c++) r.g[c] = desc->tri_p1e1e2[9 * (size_t)nd.aux + c];
+        out.leaf_recs[(size_t)k] = r;
+      }
+    });
+    if (std::getenv("RTC_TIMING")) {
+      const auto tb2 = std::chrono::steady_clock::now();
+      std::fprintf(stderr, "BVH build: tree %.1f ms, leaf records %.1f ms\n", std::chrono::duration<double, std::milli>(tb1 - tb0).count(),
+                   std::chrono::duration<double, std::milli>(tb2 - tb1).count());
     }
   }
 };
