@@ -45,3 +45,44 @@ def test_threaded_bvh_build_matches_oracle(case, pkg, prod, orc, emul, monkeypat
     assert ig["rays"] == iw["rays"]
     frac, max8, lin = compare_images(got, want, orc.quantize)
     assert frac == 1.0 and max8 == 0 and lin <= 1e-12
+
+
+def _flat_tables(pkg, flat):
+    """every table of a FlatScene as bytes"""
+    import ctypes as C
+    d = flat.desc
+    sizes = [("nodes", d.n_nodes * 32), ("xforms", d.n_xforms * 96), ("boxes", d.n_boxes * 48), ("limits", d.n_limits * 16),
+             ("tri_p1e1e2", d.n_triangles * 72), ("tri_normals", d.n_triangles * 72), ("materials", d.n_materials * 88),
+             ("patterns", d.n_patterns * 152), ("lights", d.n_lights * 48)]
+    out = {}
+    for name, nbytes in sizes:
+        ptr = getattr(d, name)
+        out[name] = C.string_at(ptr, nbytes) if nbytes else b""
+    return out
+
+
+@pytest.mark.parametrize("name,kw", [
+    ("teapot_standin", dict(width=8, height=8, segments=16, rings=12, nu=20, nv=16)),
+    ("mesh_and_spheres", dict(width=8, height=8, nx=40, nz=20, n_spheres=30)),
+    ("primitives_csg", dict(width=8, height=8)),
+    ("solids_field", dict(width=8, height=8)),
+    ("hexagon", dict(width=8, height=8)),
+    ("pattern_gallery", dict(width=8, height=8)),
+    ("cover", dict(width=8, height=8)),
+])
+@pytest.mark.parametrize("grain", [1, 7, 150])
+def test_parallel_flatten_equals_the_serial_walk(name, kw, grain, pkg, prod, monkeypatch):
+    """host/rth_flatten.hpp: worlds of 65 536 nodes and more are flattened by worker threads, job by job, and merged in
+    pre-order; every table (node records with skip / right / aux / ids / equality classes, transforms, boxes, limits,
+    triangles, materials, patterns, lights) must be byte-identical to the serial walk's. Small grains force the spine
+    pieces (groups and CSGs too big for one job) that a million-triangle world has at its top."""
+    world, cam = scenes.CONFIGS[name](prod, **kw)
+    monkeypatch.setenv("RTH_FLATTEN_THREADS", "1")
+    serial = _flat_tables(pkg, pkg.FlatScene(world))
+    monkeypatch.setenv("RTH_FLATTEN_THREADS", "4")
+    monkeypatch.setenv("RTH_FLATTEN_MIN_NODES", "0")
+    monkeypatch.setenv("RTH_FLATTEN_GRAIN", str(grain))
+    par = pkg.FlatScene(world)
+    parallel = _flat_tables(pkg, par)
+    for table in serial:
+        assert serial[table] == parallel[table], table
