@@ -944,6 +944,7 @@ inline void build_accel(const rtc_scene_desc* d, AccelBuild& A, size_t device_mi
   A.bvh.clear();
   A.leaf_recs.clear();
   std::vector<Prim> cand;
+  if (!defer && n >= 65536) cand.reserve((size_t)n);  // (growing 80 MB of candidates by doubling copies them twice over)
   FwdCache fwd_cache(d->n_xforms);
   bool cubes_ok = cube_face_families(d, A);
   if (cubes_ok && A.n_cube_dirs > 0) {
