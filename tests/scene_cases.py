@@ -16,9 +16,13 @@ SMALL_CASES = [
     ("chapter7", dict(width=64, height=32), 2),
     ("primitives_csg", dict(width=64, height=36), 8),
     ("pattern_gallery", dict(width=48, height=27), 2),
+    ("cover", dict(width=33, height=19), 1),   # odd width, cubes in the BVH (see MESH_CASES)
 ]
 MESH_CASES = [
     ("teapot_standin", dict(width=96, height=54, segments=16, rings=12, nu=20, nv=16), 1),
+    # odd width: the centre column's rays have a zero (or 1e-17) x component — the BVH's double-precision slab path
+    # (the single-precision one needs |1/d| <= 1e15 on every axis, rt_accel.cuh)
+    ("teapot_standin", dict(width=33, height=19, segments=16, rings=12, nu=20, nv=16), 1),
     ("mesh_and_spheres", dict(width=96, height=54, nx=40, nz=20, n_spheres=30), 1),
 ]
 
