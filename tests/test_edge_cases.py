@@ -253,3 +253,65 @@ def test_device_built_bvh_matches_oracle(case, pkg, prod, orc, monkeypatch):
         frac, max8, lin = compare_images(got, want, orc.quantize)
         assert frac >= 0.999 and max8 <= 1 and lin <= 1e-12, (kwr, frac, max8, lin)
     ds.close()
+
+
+def _far_cluster(api, pkg, centre, extent, n_tri=300, n_sph=40, n_cube=12, seed=7):
+    """small triangles, spheres and cubes in a cluster of size `extent` around `centre` (far from the world origin when
+    |centre| >> extent: the regime where a single-precision box test is coarsest), seen from just outside it"""
+    T = pkg.transform
+    rng = np.random.default_rng(seed)
+    w = api.world()
+    c = np.asarray(centre, dtype=np.float64)
+    w.add_light(tuple(c + extent * np.array([-2.0, 3.0, -4.0])), (1.0, 1.0, 1.0))
+    p0 = c + extent * rng.uniform(-1.0, 1.0, size=(n_tri, 1, 3))
+    pts = p0 + 0.15 * extent * rng.uniform(-1.0, 1.0, size=(n_tri, 3, 3))
+    nrm = np.tile(np.array([[[0.0, 1.0, 0.0]]]), (n_tri, 3, 1))
+    mesh = api.group()
+    mesh.add_triangles(np.ascontiguousarray(pts), np.ascontiguousarray(nrm))
+    mesh.set_material(pkg.Material(color=(0.8, 0.5, 0.3), reflective=0.3))
+    w.add_object(mesh)
+    for k in range(n_sph):
+        p = c + extent * rng.uniform(-1.0, 1.0, size=3)
+        r = extent * rng.uniform(0.03, 0.12)
+        mat = pkg.Material(color=(0.3, 0.6, 0.9), reflective=0.5) if k % 2 else pkg.Material(
+            color=(0.1, 0.1, 0.1), transparency=0.9, reflective=0.9, refractive_index=1.5)
+        w.add_object(api.sphere().set_transform(T.matmul(T.translation(*p), T.scaling(r, r, r))).set_material(mat))
+    for k in range(n_cube):
+        p = c + extent * rng.uniform(-1.0, 1.0, size=3)
+        r = extent * rng.uniform(0.05, 0.1)
+        w.add_object(api.cube().set_transform(T.chain(T.scaling(r, r, r), T.rotation_y(0.3 * k), T.translation(*p)))
+                     .set_material(pkg.Material(color=(0.9, 0.9, 0.2))))
+    cam = api.camera(48, 48, 0.9)
+    cam.set_transform(T.view_transform(tuple(c + extent * np.array([0.3, 0.8, -3.5])), tuple(c), (0, 1, 0)))
+    return w, cam
+
+
+FAR_CLUSTERS = [((0.0, 0.0, 0.0), 1.0), ((5000.0, -3000.0, 8000.0), 5.0), ((3.0e6, 1.0e6, -2.0e6), 40.0),
+                ((0.5, 0.5, 0.5), 0.8), ((-70000.0, 10.0, 0.5), 0.8)]
+
+
+@pytest.mark.parametrize("centre,extent", FAR_CLUSTERS, ids=lambda v: str(v))
+def test_single_precision_boxes_never_lose_a_hit_kernel_source(centre, extent, pkg, prod, emul):
+    """rt_accel.cuh Slab32: the BVH's boxes and slab test are single precision, widened by a bound on their own rounding
+    that grows with the tree's distance from the origin. Accelerated search == the reference's own traversal, bit for
+    bit, on clusters at the origin and thousands and millions of units away from it (shapes no smaller than the
+    reference's matrix inverse accepts: |det| >= 1e-5)."""
+    w, cam = _far_cluster(prod, pkg, centre, extent)
+    flat = pkg.FlatScene(w)
+    want, iw = emul.render(cam, w, flat=flat, faithful=True)
+    got, ig = emul.render(cam, w, flat=flat, faithful=False)
+    assert ig["rays"] == iw["rays"] and ig["rays"] > 48 * 48
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("centre,extent", FAR_CLUSTERS, ids=lambda v: str(v))
+def test_single_precision_boxes_never_lose_a_hit_gpu(centre, extent, pkg, prod):
+    w, cam = _far_cluster(prod, pkg, centre, extent)
+    ds = pkg.DeviceScene(pkg.FlatScene(w))
+    want, sw = ds.render(cam, faithful=True)
+    got, sg = ds.render(cam, wavefront=False)
+    got2, sg2 = ds.render(cam, wavefront=True)
+    ds.close()
+    assert sg.rays == sw.rays and sg2.rays == sw.rays
+    assert np.array_equal(got, want) and np.array_equal(got2, want)
