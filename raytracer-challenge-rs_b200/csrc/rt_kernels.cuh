@@ -10,6 +10,12 @@
 #ifndef RTK_MIN_BLOCKS
 #define RTK_MIN_BLOCKS 4
 #endif
+// resident CTAs per SM of the kernels with the BVH traversal and the generic leaf tests in them (no CSG): three, i.e.
+// 168 registers — the search's state spills at 128 (profiles/r02bd_min_blocks.log: teapot 1.50 -> 1.34 ms, cover 2.87 ->
+// 2.55 ms with three, 1.57 / 2.77 with two, 1.71 / 3.05 with five; the CSG kernels do not care, the lean kernel wants four)
+#ifndef RTK_BVH_MINB
+#define RTK_BVH_MINB 3
+#endif
 // resident CTAs per SM of the kernels launched for accelerators far beyond L2 (rtc_scene::big_accel)
 #ifndef RTK_BIG_MINB
 #define RTK_BIG_MINB 8

@@ -301,11 +301,11 @@ int launch_rows(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool fa
       render_kernel<false, 2><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
     } else if (s->tri_sph_only && !faithful) {
       if (s->big_accel) render_kernel<false, 4, RTK_BIG_MINB><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
-      else render_kernel<false, 4><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
+      else render_kernel<false, 4, RTK_BVH_MINB><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
     } else {
       if (faithful) render_kernel<false, true><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
       else if (s->big_accel) render_kernel<false, false, RTK_BIG_MINB><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
-      else render_kernel<false, false><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
+      else render_kernel<false, false, RTK_BVH_MINB><<<grid, block, 0, stream>>>(s->view, cam, Pk, out, s->d_counters);
     }
     s->launches++;
   }
@@ -427,10 +427,10 @@ int launch_wave(rtc_scene* s, const CameraD& cam, const RenderParams& P, double*
       launch_wave_level<false, RTK_MIN_BLOCKS, 2>(s, cam, P, A, L == 0, out, stream);
     } else if (s->tri_sph_only) {
       if (s->big_accel) launch_wave_level<false, RTK_BIG_MINB, 4>(s, cam, P, A, L == 0, out, stream);
-      else launch_wave_level<false, RTK_MIN_BLOCKS, 4>(s, cam, P, A, L == 0, out, stream);
+      else launch_wave_level<false, RTK_BVH_MINB, 4>(s, cam, P, A, L == 0, out, stream);
     } else {
       if (s->big_accel) launch_wave_level<false, RTK_BIG_MINB>(s, cam, P, A, L == 0, out, stream);
-      else launch_wave_level<false, RTK_MIN_BLOCKS>(s, cam, P, A, L == 0, out, stream);
+      else launch_wave_level<false, RTK_BVH_MINB>(s, cam, P, A, L == 0, out, stream);
     }
   }
   for (int L = D - 1; L >= 0; L--) {
@@ -493,7 +493,7 @@ int launch_stream(rtc_scene* s, const CameraD& cam, const RenderParams& P, doubl
 #if defined(RTK_STREAM_STATS)
   CUDA_TRY(cudaMemsetAsync(s->d_counters + 8, 0, 16 * sizeof(unsigned long long), stream));
 #endif
-  const int minb = s->big_accel ? RTK_BIG_MINB : RTK_MIN_BLOCKS;
+  const int minb = s->big_accel ? RTK_BIG_MINB : ((s->has_csg || s->lean) ? RTK_MIN_BLOCKS : RTK_BVH_MINB);
   const int grid = s->sm_count * minb;
   if (s->has_csg) {
     if (s->big_accel) wave_stream_kernel<true, RTK_BIG_MINB><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
@@ -502,10 +502,10 @@ int launch_stream(rtc_scene* s, const CameraD& cam, const RenderParams& P, doubl
     wave_stream_kernel<false, RTK_MIN_BLOCKS, 2><<<s->sm_count * RTK_MIN_BLOCKS, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
   } else if (s->tri_sph_only) {
     if (s->big_accel) wave_stream_kernel<false, RTK_BIG_MINB, 4><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
-    else wave_stream_kernel<false, RTK_MIN_BLOCKS, 4><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+    else wave_stream_kernel<false, RTK_BVH_MINB, 4><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
   } else {
     if (s->big_accel) wave_stream_kernel<false, RTK_BIG_MINB><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
-    else wave_stream_kernel<false, RTK_MIN_BLOCKS><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
+    else wave_stream_kernel<false, RTK_BVH_MINB><<<grid, 128, 0, stream>>>(s->view, cam, P, A, out, s->d_counters);
   }
   s->launches++;
   CUDA_TRY(cudaGetLastError());
