@@ -128,9 +128,9 @@ def orc(pkg):
 class Emul:
     """tests/cpu_emul/libemul.so — the kernel source compiled for the host (test-only)."""
 
-    def __init__(self, pkg):
+    def __init__(self, pkg, path=None):
         self.pkg = pkg
-        self.lib = C.CDLL(os.path.join(ROOT, "tests", "cpu_emul", "libemul.so"))
+        self.lib = C.CDLL(path or os.path.join(ROOT, "tests", "cpu_emul", "libemul.so"))
         vp = C.c_void_p
         self.lib.emul_render.argtypes = [vp, vp, vp, C.c_uint, vp, vp]
         self.lib.emul_trace_rays.argtypes = [vp, C.c_size_t, vp, vp, C.c_uint32, vp, vp]

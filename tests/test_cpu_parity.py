@@ -2,11 +2,12 @@
 oracle, bit for bit, on small frames. Proves traversal/CSG/containers/iterative-recursion logic and
 the host mirror before GPU time is spent; the GPU tier repeats the same cases through the C-ABI."""
 import importlib
+import os
 
 import numpy as np
 import pytest
 
-from conftest import compare_images
+from conftest import ROOT, compare_images
 from scene_cases import MESH_CASES, SMALL_CASES, case_id
 
 scenes = importlib.import_module("raytracer-challenge-rs_b200.scenes")
@@ -86,3 +87,24 @@ def test_parallel_flatten_equals_the_serial_walk(name, kw, grain, pkg, prod, mon
     parallel = _flat_tables(pkg, par)
     for table in serial:
         assert serial[table] == parallel[table], table
+
+
+@pytest.mark.parametrize("flags", [["-DRTK_BVH_WIDE=1"], ["-DRTK_BVH_F32=0"]], ids=["four_children_per_node", "double_precision_nodes"])
+def test_flagged_bvh_variants_still_match_the_oracle(flags, pkg, prod, orc, tmp_path):
+    """The measured-and-shelved BVH layouts stay compilable and correct: the kernel source is compiled for the host with
+    the variant's flag (four-child collapsed nodes; the 128-byte double-precision nodes of rounds 1-2) and must render
+    the mesh cases like the oracle, bit for bit."""
+    import subprocess
+    from conftest import Emul
+    so = str(tmp_path / "libemul_variant.so")
+    subprocess.run(["g++", "-O1", "-std=c++17", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-pthread", "-shared"] + flags +
+                   ["-o", so, os.path.join(ROOT, "tests", "cpu_emul", "emul.cpp")], check=True)
+    variant = Emul(pkg, so)
+    for name, kw, aa in MESH_CASES[:2] + [("cover", dict(width=64, height=36), 1)]:
+        wo, co = scenes.CONFIGS[name](orc.api, **kw)
+        wp, cp = scenes.CONFIGS[name](prod, **kw)
+        want, iw = orc.render(co, wo, aa=aa, threads=0)
+        got, ig = variant.render(cp, wp, aa=aa, faithful=False)
+        assert ig["rays"] == iw["rays"], name
+        frac, max8, lin = compare_images(got, want, orc.quantize)
+        assert frac == 1.0 and max8 == 0 and lin <= 1e-12, name
