@@ -234,7 +234,7 @@ RTC_HD void search(const SceneView& S, const RayD& ray, Query& C, CsgScratch* cs
 #if defined(RTK_SHARED_STACK) && defined(__CUDA_ARCH__)
     constexpr int SH_N = RTK_SHARED_STACK;
     __shared__ int32_t sh_node[SH_N][128];
-    __shared__ double sh_tmin[SH_N][128];
+    __shared__ bvh_real sh_tmin[SH_N][128];
     const int sh_t = threadIdx.x & 127;
 #define RTK_ST_NODE(k) ((k) < SH_N ? sh_node[(k)][sh_t] : st->node[(k) - SH_N])
 #define RTK_ST_TMIN(k) ((k) < SH_N ? sh_tmin[(k)][sh_t] : st->tmin[(k) - SH_N])
