@@ -533,6 +533,9 @@ bool use_wavefront(const rtc_scene* s, const RenderParams& P, bool faithful, uin
   if (flags & RTC_OPT_WAVEFRONT) return true;
   // ... and on accelerators far beyond L2 the wavefront wins even on a whole frame (1 M triangles at 4K: 55.1 vs
   // 62.3 ms): its passes are all-reflection / all-refraction warps of compacted rays, which traverse together
+  // (mirror-only scenes — the OBJ stand-in — recurse in chains and never take the wavefront: a shard of them is one
+  // silhouette warp's chain either way; forced through it, one GPU as rank 0 of 4 / 8 needs 1.66 / 1.55 ms with the
+  // passes and 1.34 / 1.28 ms streaming against 1.09 / 1.06 ms recursive, profiles/r02bs_shard_probe_others.log)
   return s->has_branching && (P.nranks >= RTK_WAVE_MIN_RANKS || s->big_accel);
 }
 
@@ -558,7 +561,9 @@ int launch_frame(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool f
     // every share). A frame it gives up on is rendered again recursively like an overflowed one.
     static const char* env_stream = std::getenv("RTC_WAVE_STREAM");
     const bool streaming = env_stream ? env_stream[0] == '1'
-                                      : ((P.flags & RTC_OPT_WAVE_STREAM) != 0 || (s->big_accel && P.nranks >= RTK_STREAM_MIN_RANKS));
+                                      : ((P.flags & RTC_OPT_WAVE_STREAM) != 0 || (s->big_accel && P.nranks >= RTK_STREAM_MIN_RANKS) ||
+                                         // (a BVH of generic shapes, cover.yml, an eighth of the frame: 0.65 ms against 0.72 / 0.79)
+                                         (!s->lean && !s->has_csg && !s->tri_sph_only && P.nranks >= 8));
     rc = streaming ? launch_stream(s, cam, P, out, stream) : launch_wave(s, cam, P, out, stream);
   } else {
     rc = launch_rows(s, cam, P, faithful, out, stream, 0, 0);
