@@ -314,7 +314,7 @@ int launch_rows(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool fa
 }
 
 #ifndef RTK_STREAM_MIN_RANKS
-#define RTK_STREAM_MIN_RANKS 4
+#define RTK_STREAM_MIN_RANKS 2
 #endif
 
 // Scratch arenas are big (GBs at 4K): keep one freed arena per device, like the canvases.
@@ -554,10 +554,10 @@ int launch_frame(rtc_scene* s, const CameraD& cam, const RenderParams& P, bool f
   if (s->last_wave) {
     s->last_cam = cam; s->last_P = P; s->last_out = out;
     // the level-synchronous passes (rt_wave.cuh), or one barrier-free persistent launch (rt_stream.cuh): on request,
-    // and by default for a quarter or less of a frame over an accelerator far beyond L2 — there a level's tail is
+    // and by default for half or less of a frame over an accelerator far beyond L2 — there a level's tail is
     // long (a few heavy traversals) and the next level's rays are ready to fill it (one GPU rendering rank 0's share
     // of the million-triangle 4K frame, profiles/r02bo_shard_probe_mesh.log: a quarter 13.5 -> 12.0 ms, an eighth
-    // 8.9 -> 7.2 ms; half a frame 22.3 -> 21.9, the whole frame 39.7 -> 40.7; on the glass scene the passes win at
+    // 8.9 -> 7.2 ms; half a frame 22.3 -> 21.9 (two GPUs: 22.7 -> 22.1), the whole frame 39.7 -> 40.7; on the glass scene the passes win at
     // every share). A frame it gives up on is rendered again recursively like an overflowed one.
     static const char* env_stream = std::getenv("RTC_WAVE_STREAM");
     const bool streaming = env_stream ? env_stream[0] == '1'
